@@ -1,0 +1,143 @@
+/* tasi_gpu.h — C ABI of the B200 cost-propagation core for the three grid replanners of
+ * roncapat/UNIGE-TASI-path-planners (FD*, MS-DFM, MFD*).
+ *
+ * The reference has no FFI layer: its operator API for this path is the public surface of
+ * ReplannerBase<Derived,Elem,Info,Key> (ProjectToolkit/include/ReplannerBase.h:29-161). Each entry point
+ * below replaces one member of that class (cited per function); the C++ classes in
+ * unige_tasi_path_planners_b200/host/GpuPlanners.h rebuild the class surface on top of it.
+ *
+ * Conventions (ProjectToolkit/Graph.cpp:22-34): the map is `length` rows (x, north to south) by `width`
+ * columns (y) of uint8 traversal costs, map[x*width + y]; a byte >= the occupancy threshold is an obstacle.
+ * FD* and MFD* values live on the (length+1) x (width+1) nodes, MS-DFM values on the length x width cells;
+ * "element" means node or cell accordingly. Values are float32, +INF = unreachable.
+ *
+ * All functions return an int status: TASI_OK, the reference's step() codes, or a negative error; no C++
+ * exception crosses this boundary. One handle owns one CUDA stream on one device; calls on a handle must be
+ * serialised by the caller, different handles are independent. There is no CPU fallback: without a CUDA
+ * device tasi_create fails with TASI_ERR_CUDA.
+ */
+#ifndef TASI_GPU_H
+#define TASI_GPU_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TASI_OK 0
+#define TASI_LOOP_FAILURE_NO_GRAPH (-1) /* ReplannerBase.h:23 */
+#define TASI_LOOP_FAILURE_NO_GOAL (-2)  /* ReplannerBase.h:24 */
+#define TASI_ERR_ARG (-3)
+#define TASI_ERR_CUDA (-4)
+#define TASI_ERR_TIMEOUT (-5) /* the solver's device watchdog fired */
+#define TASI_ERR_STATE (-6)
+
+#define TASI_FD 0  /* FieldDPlanner<O>        FieldDStar/FieldDPlanner.h */
+#define TASI_DFM 1 /* DFMPlanner<O>           DynamicFastMarching/DynamicFastMarching.h */
+#define TASI_MFD 2 /* ShiftedGridPlanner<O>   ShiftedGridFastMarching/ShiftedGridPlanner.h */
+
+typedef struct tasi_planner tasi_planner;
+
+/* Work counters of the last step() (the tile-revisit evidence BASELINE.json asks for). */
+typedef struct tasi_stats {
+    uint64_t tiles;            /* 32x32 tiles of the element grid */
+    uint64_t tile_visits;      /* tiles staged into shared memory (solve phase) */
+    uint64_t tile_rounds;      /* in-tile relaxation rounds (4 directional sweeps each) */
+    uint64_t elem_lowered;     /* accepted decreases of an element value */
+    uint64_t queue_pushes;     /* tile activations that entered the work queue */
+    uint64_t inval_visits;     /* tile visits of the invalidate phase of a replan */
+    uint64_t elem_invalidated; /* elements reset to INF by the invalidate phase */
+    uint64_t seed_elems;       /* elements seeded by the last patch (== num_nodes_updated) */
+    float kernel_ms_solve;     /* CUDA-event time of the solver kernel(s), re-propagation phase */
+    float kernel_ms_inval;     /* CUDA-event time of the invalidate phase */
+    float kernel_ms_init;      /* field fill / seeding kernels */
+    int32_t solver_blocks;     /* persistent CTAs launched */
+    int32_t solver_launches;   /* kernels launched by the last step() */
+} tasi_stats;
+
+/* Planner object. kind = TASI_FD|TASI_DFM|TASI_MFD; level = the reference's OPT_LVL template argument
+ * (0/1, MFD* also 2): all levels of a planner have the same fixed point, so they share one kernel.
+ * Replaces: `FieldDPlanner<OPT_LVL> planner{}` (Tests/Planners/FDSTAR/main.cpp:77). */
+int tasi_create(int kind, int level, int device, tasi_planner **out);
+int tasi_destroy(tasi_planner *p);
+
+/* ReplannerBase::reset (ReplannerBase.h:39-41): the next step() re-initialises the search. */
+int tasi_reset(tasi_planner *p);
+
+/* ReplannerBase::set_occupancy_threshold -> Graph::set_occupancy_threshold (Graph.cpp:18-20):
+ * threshold byte = (unsigned char)(t * 255). Default 254 (Graph.h:33). */
+int tasi_set_occupancy_threshold(tasi_planner *p, float t);
+
+/* ReplannerBase::set_heuristic_multiplier (ReplannerBase.h:81-83). Stored; the heuristic only prunes the
+ * reference's expansion order and never changes a settled value, so the solver ignores it. */
+int tasi_set_heuristic_multiplier(tasi_planner *p, float mult);
+
+/* ReplannerBase::set_map -> Graph::init (ReplannerBase.h:85-88, Graph.cpp:22-29). Copies the host map to the
+ * device during the call; the host pointer is not retained. */
+int tasi_set_map(tasi_planner *p, const uint8_t *host_map, int width, int length);
+
+/* Same, from a buffer already resident in device memory (row pitch in bytes). */
+int tasi_set_map_device(tasi_planner *p, const uint8_t *dev_map, int width, int length, int64_t pitch);
+
+/* ReplannerBase::patch_map -> Graph::update (ReplannerBase.h:90-92, Graph.cpp:36-51): rows x..x+h-1, columns
+ * y..y+w-1 take the bytes of `patch` (h rows of w); cells whose byte changed seed the next replan.
+ * n_changed (optional) receives the number of changed cells. */
+int tasi_patch_map(tasi_planner *p, const uint8_t *host_patch, int x, int y, int w, int h, uint64_t *n_changed);
+
+/* ReplannerBase::set_start / set_goal (ReplannerBase.h:94-108; Graph.cpp:6-16). Positions are rounded to
+ * the element with roundf (Node.cpp:14-17, Cell.cpp:20-21). A goal on a different element forces re-init. */
+int tasi_set_start(tasi_planner *p, float x, float y);
+int tasi_set_goal(tasi_planner *p, float x, float y);
+
+/* ReplannerBase::step (ReplannerBase.h:43-75): initial plan, or two-phase repair after patches; returns when
+ * the field is converged. Outputs (all optional): u_ms/p_ms = host wall time of the update and plan halves
+ * (the reference's u_time/p_time), n_updated/n_expanded = num_nodes_updated/num_nodes_expanded. */
+int tasi_step(tasi_planner *p, float *u_ms, float *p_ms, uint64_t *n_updated, uint64_t *n_expanded);
+
+/* Element-grid extents: (length+1, width+1) for FD and MFD, (length, width) for MS-DFM. */
+int tasi_field_dims(tasi_planner *p, int *ex, int *ey);
+
+/* Hand-off to the path extractor: what ExpandedMap::get_g / get_rhs return after convergence
+ * (ExpandedMap_impl.h:65-85; g == rhs on a converged field). read_window copies elements
+ * [x0,x0+nx) x [y0,y0+ny) (row-major into out, INF outside the grid); read_field the whole grid. */
+int tasi_read_window(tasi_planner *p, int x0, int y0, int nx, int ny, float *host_out);
+int tasi_read_field(tasi_planner *p, float *host_out);
+
+/* Device view of the converged field: pointer to element (0,0) and row pitch in elements. */
+int tasi_field_device(tasi_planner *p, float **dev_ptr, int64_t *pitch_elems);
+/* Device view of the cost grid: pointer to cell (0,0) and row pitch in bytes. */
+int tasi_cost_device(tasi_planner *p, uint8_t **dev_ptr, int64_t *pitch_bytes);
+
+/* Deterministic synthetic map generated on the device (same function as synth.py / SURVEY.md 8d):
+ * rows [row0,row0+length) of the unbounded map of width `width`; 9x9 blocks of cost 1 are cleared around
+ * (sx,sy) and (gx,gy) given in GLOBAL cell coordinates (negative = none). Then behaves as set_map. */
+int tasi_synth_map(tasi_planner *p, uint64_t seed, int width, int length, int64_t row0, int p_obs, int sx, int sy,
+                   int gx, int gy);
+/* Copies the device cost grid back (length*width bytes). */
+int tasi_read_map(tasi_planner *p, uint8_t *host_out);
+
+int tasi_get_stats(tasi_planner *p, tasi_stats *out);
+const char *tasi_last_error(tasi_planner *p);
+
+/* ---- row-band sharding (one band per GPU; halo rows are exchanged by the caller, e.g. NCCL send/recv) ----
+ * A band holds element rows [0,ex) of its own plus one halo row above (row -1) and below (row ex) in the
+ * same device array. tasi_band_config marks which sides are open (have a neighbour band) and gives the
+ * band's first global element row so start/goal can be given in global coordinates. The band's map must
+ * then contain one extra cost row per open side (the cells between the halo row and the first owned row). */
+int tasi_band_config(tasi_planner *p, int64_t global_row0, int open_top, int open_bottom);
+/* Device pointers of the rows to send (first/last owned row) and to receive into (staging rows);
+ * each is `count` floats. side 0 = top, 1 = bottom. */
+int tasi_band_rows(tasi_planner *p, int side, float **send_row, float **recv_stage, int64_t *count);
+/* Merge the received staging row into the halo (min), activate the border tiles whose halo got lower;
+ * n_lowered = how many halo elements changed. */
+int tasi_band_import(tasi_planner *p, int side, uint64_t *n_lowered);
+/* Initialise the field (INF, goal = 0 if the goal lies in this band) without solving. */
+int tasi_band_begin(tasi_planner *p);
+/* Drain the local work queue to convergence; n_active_out = tiles processed. */
+int tasi_band_solve(tasi_planner *p, uint64_t *n_tile_visits);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TASI_GPU_H */

@@ -1,0 +1,174 @@
+"""GPU parity: the CUDA solver (through the C ABI) against the CPU oracle on the same seeded inputs.
+
+Bars (BASELINE.json north_star): reachability masks identical; FD*/MFD* fields bit-exact with the oracle
+(their fixed point is order-independent); MS-DFM within 1e-4 relative (observed ~1e-7).
+"""
+import numpy as np
+import pytest
+
+from unige_tasi_path_planners_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+KINDS = [0, 1, 2]
+REL_TOL = 1e-4  # north_star: converged value field within 1e-4 relative
+
+
+def make(kind, level=None):
+    from unige_tasi_path_planners_b200 import PLANNERS
+    cls = PLANNERS[kind]
+    return cls(cls.max_level if level is None else level)
+
+
+def compare(kind, got, want, exact=None):
+    assert got.shape == want.shape
+    fin_g, fin_w = np.isfinite(got), np.isfinite(want)
+    assert np.array_equal(fin_g, fin_w), "reachability masks differ at %d elements" % (fin_g != fin_w).sum()
+    if exact is None:
+        exact = kind != 1
+    if exact:
+        bad = got[fin_w] != want[fin_w]
+        assert not bad.any(), "%d of %d elements not bit-exact, max rel %g" % (
+            bad.sum(), fin_w.sum(), np.max(np.abs(got[fin_w] - want[fin_w]) / np.maximum(want[fin_w], 1e-30)))
+    else:
+        rel = np.abs(got[fin_w] - want[fin_w]) / np.maximum(np.abs(want[fin_w]), 1e-30)
+        assert rel.max(initial=0.0) <= REL_TOL, "max rel err %g" % rel.max()
+
+
+def plan(kind, cmap, start, goal, occ=1.0):
+    p = make(kind)
+    p.set_occupancy_threshold(occ)
+    p.set_map(cmap)
+    p.set_start(*start)
+    p.set_goal(*goal)
+    assert p.step() == 0
+    return p
+
+
+@pytest.mark.parametrize("kind", KINDS)
+@pytest.mark.parametrize("shape", [(64, 64), (100, 37), (33, 200), (31, 31), (256, 256), (1, 1), (5, 70)])
+def test_initial_plan_matches_oracle(oracle, kind, shape):
+    L, W = shape
+    start, goal = (min(5.0, L - 1), min(5.0, W - 1)), (float(max(L - 6, 0)), float(max(W - 6, 0)))
+    cmap = synth.synth_map(11 + kind, L, W, 10, start, goal)
+    p = plan(kind, cmap, start, goal)
+    got = p.read_field()
+    want = oracle.solve(kind, cmap, goal)
+    compare(kind, got, want)
+    lo, hi, _ = oracle.residual(kind, cmap, goal, got)
+    assert lo == 0  # nothing can still be lowered: a true fixed point of the reference's operator
+    if kind != 1:
+        assert hi == 0
+
+
+@pytest.mark.parametrize("kind", KINDS)
+@pytest.mark.parametrize("p_obs", [0, 30, 45])
+def test_obstacle_density(oracle, kind, p_obs):
+    L = W = 160
+    start, goal = (5.0, 5.0), (80.0, 80.0)
+    cmap = synth.synth_map(21, L, W, p_obs, start, goal)
+    p = plan(kind, cmap, start, goal)
+    compare(kind, p.read_field(), oracle.solve(kind, cmap, goal))
+
+
+@pytest.mark.parametrize("kind", KINDS)
+def test_occupancy_threshold_and_uniform(oracle, kind):
+    L, W = 96, 130
+    cmap = np.full((L, W), 7, np.uint8)
+    cmap[40:44, 10:120] = 200  # a wall once the threshold is 0.5 (>= 127)
+    start, goal = (3.0, 3.0), (90.0, 64.0)
+    p = plan(kind, cmap, start, goal, occ=0.5)
+    thr = int(0.5 * 255.0)
+    compare(kind, p.read_field(), oracle.solve(kind, cmap, goal, thr=thr))
+
+
+@pytest.mark.parametrize("kind", KINDS)
+def test_unreachable_goal_pocket(oracle, kind):
+    L = W = 80
+    cmap = np.full((L, W), 3, np.uint8)
+    cmap[30:51, 30] = 255; cmap[30:51, 50] = 255; cmap[30, 30:51] = 255; cmap[50, 30:51] = 255
+    start, goal = (5.0, 5.0), (40.0, 40.0)
+    p = plan(kind, cmap, start, goal)
+    got = p.read_field()
+    compare(kind, got, oracle.solve(kind, cmap, goal))
+    assert not np.isfinite(got[5, 5])
+
+
+@pytest.mark.parametrize("kind", KINDS)
+def test_step_return_codes(kind):
+    p = make(kind)
+    assert p.step() == -1  # LOOP_FAILURE_NO_GRAPH
+    p.set_map(np.ones((8, 8), np.uint8))
+    assert p.step() == -2  # LOOP_FAILURE_NO_GOAL
+    p.set_goal(4.0, 4.0)
+    p.set_start(1.0, 1.0)
+    assert p.step() == 0
+
+
+@pytest.mark.parametrize("kind", KINDS)
+@pytest.mark.parametrize("mode", ["mixed", "raise", "lower"])
+def test_replan_equals_from_scratch(oracle, kind, mode):
+    """Two-phase repair after a patch == from-scratch solve of the patched map."""
+    L = W = 200
+    start, goal = (5.0, 5.0), (float(L - 6), float(W - 6))
+    cmap = synth.synth_map(31, L, W, 10, start, goal)
+    p = plan(kind, cmap, start, goal)
+    rng = np.random.default_rng(5)
+    x, y, h, w = 60, 70, 48, 40
+    old = cmap[x:x + h, y:y + w]
+    if mode == "mixed":
+        patch = synth.synth_rows(977, 0, h, w, 15)
+    elif mode == "raise":
+        patch = np.where(rng.random((h, w)) < 0.3, 255, np.minimum(old.astype(int) + 9, 255)).astype(np.uint8)
+    else:
+        patch = np.maximum(old.astype(int) // 2, 1).astype(np.uint8)
+    n_changed = p.patch_map(patch, x, y)
+    cm2 = cmap.copy()
+    assert n_changed == oracle.patch(cm2, patch, x, y)
+    assert np.array_equal(p.read_map(), cm2)
+    p.set_start(8.0, 8.0)
+    assert p.step() == 0
+    assert p.num_nodes_updated > 0
+    compare(kind, p.read_field(), oracle.solve(kind, cm2, goal))
+    # a second, disjoint patch on top
+    patch2 = synth.synth_rows(1234, 0, 20, 33, 25)
+    p.patch_map(patch2, 150, 20)
+    oracle.patch(cm2, patch2, 150, 20)
+    p.set_start(9.0, 9.0)
+    assert p.step() == 0
+    compare(kind, p.read_field(), oracle.solve(kind, cm2, goal))
+
+
+@pytest.mark.parametrize("kind", KINDS)
+def test_new_goal_reinitialises(oracle, kind):
+    L = W = 120
+    cmap = synth.synth_map(41, L, W, 10, (5, 5), (100, 100))
+    p = plan(kind, cmap, (5.0, 5.0), (100.0, 100.0))
+    p.set_goal(20.0, 90.0)
+    assert p.step() == 0
+    compare(kind, p.read_field(), oracle.solve(kind, cmap, (20.0, 90.0)))
+    f1 = p.read_field()
+    p.set_goal(20.2, 89.9)  # same element: no re-init, nothing to do
+    assert p.step() == 0
+    assert np.array_equal(f1, p.read_field())
+
+
+@pytest.mark.parametrize("kind", KINDS)
+def test_window_read(kind):
+    L, W = 70, 90
+    cmap = synth.synth_map(51, L, W, 5, (5, 5), (60, 80))
+    p = plan(kind, cmap, (5.0, 5.0), (60.0, 80.0))
+    f = p.read_field()
+    w = p.read_window(-3, 80, 10, 20)
+    ex, ey = f.shape
+    ref = np.full((10, 20), np.inf, np.float32)
+    ref[3:, :ey - 80] = f[0:7, 80:ey]
+    assert np.array_equal(w, ref)
+
+
+def test_device_synth_map_matches_host():
+    from unige_tasi_path_planners_b200 import DFMPlanner
+    p = DFMPlanner(1)
+    p.synth_map(77, 300, 130, row0=0, p_obs=10, start=(5, 5), goal=(120, 290))
+    host = synth.synth_map(77, 130, 300, 10, (5, 5), (120, 290))
+    assert np.array_equal(p.read_map(), host)

@@ -1,0 +1,108 @@
+"""ctypes binding of the C ABI declared in include/tasi_gpu.h (libtasi_gpu.so, built by build.py).
+
+There is no fallback: if the library is missing, or no CUDA device is present when a planner is created, the
+call raises.
+"""
+import ctypes as C
+import os
+
+PKG = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(PKG, "libtasi_gpu.so")
+HOSTOPS_PATH = os.path.join(PKG, "libtasi_hostops.so")
+
+OK = 0
+LOOP_OK = 0
+LOOP_FAILURE_NO_GRAPH = -1
+LOOP_FAILURE_NO_GOAL = -2
+ERR_ARG, ERR_CUDA, ERR_TIMEOUT, ERR_STATE = -3, -4, -5, -6
+FD, DFM, MFD = 0, 1, 2
+
+_u8p = C.POINTER(C.c_uint8)
+_f32p = C.POINTER(C.c_float)
+_u64p = C.POINTER(C.c_uint64)
+_i64p = C.POINTER(C.c_int64)
+_ip = C.POINTER(C.c_int)
+
+
+class Stats(C.Structure):
+    _fields_ = [("tiles", C.c_uint64), ("tile_visits", C.c_uint64), ("tile_rounds", C.c_uint64),
+                ("elem_lowered", C.c_uint64), ("queue_pushes", C.c_uint64), ("inval_visits", C.c_uint64),
+                ("elem_invalidated", C.c_uint64), ("seed_elems", C.c_uint64), ("kernel_ms_solve", C.c_float),
+                ("kernel_ms_inval", C.c_float), ("kernel_ms_init", C.c_float), ("solver_blocks", C.c_int32),
+                ("solver_launches", C.c_int32)]
+
+    def as_dict(self):
+        return {n: getattr(self, n) for n, _ in self._fields_}
+
+
+# every symbol include/tasi_gpu.h declares: name -> (restype, argtypes)
+SIGNATURES = {
+    "tasi_create": (C.c_int, [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_void_p)]),
+    "tasi_destroy": (C.c_int, [C.c_void_p]),
+    "tasi_reset": (C.c_int, [C.c_void_p]),
+    "tasi_set_occupancy_threshold": (C.c_int, [C.c_void_p, C.c_float]),
+    "tasi_set_heuristic_multiplier": (C.c_int, [C.c_void_p, C.c_float]),
+    "tasi_set_map": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int]),
+    "tasi_set_map_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int64]),
+    "tasi_patch_map": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, _u64p]),
+    "tasi_set_start": (C.c_int, [C.c_void_p, C.c_float, C.c_float]),
+    "tasi_set_goal": (C.c_int, [C.c_void_p, C.c_float, C.c_float]),
+    "tasi_step": (C.c_int, [C.c_void_p, _f32p, _f32p, _u64p, _u64p]),
+    "tasi_field_dims": (C.c_int, [C.c_void_p, _ip, _ip]),
+    "tasi_read_window": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),
+    "tasi_read_field": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "tasi_field_device": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), _i64p]),
+    "tasi_cost_device": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), _i64p]),
+    "tasi_synth_map": (C.c_int, [C.c_void_p, C.c_uint64, C.c_int, C.c_int, C.c_int64, C.c_int, C.c_int, C.c_int,
+                                 C.c_int, C.c_int]),
+    "tasi_read_map": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "tasi_get_stats": (C.c_int, [C.c_void_p, C.POINTER(Stats)]),
+    "tasi_last_error": (C.c_char_p, [C.c_void_p]),
+    "tasi_band_config": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, C.c_int]),
+    "tasi_band_rows": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), _i64p]),
+    "tasi_band_import": (C.c_int, [C.c_void_p, C.c_int, _u64p]),
+    "tasi_band_begin": (C.c_int, [C.c_void_p]),
+    "tasi_band_solve": (C.c_int, [C.c_void_p, _u64p]),
+}
+
+_lib = None
+
+
+def lib():
+    """The loaded CUDA library. Raises if it has not been built (python -m unige_tasi_path_planners_b200.build)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                "CUDA extension missing: %s (build it with `python -m unige_tasi_path_planners_b200.build`); "
+                "there is no CPU fallback" % LIB_PATH)
+        L = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(L, name)  # AttributeError if the library does not export a declared symbol
+            fn.restype = res
+            fn.argtypes = args
+        _lib = L
+    return _lib
+
+
+_hostops = None
+
+
+def hostops():
+    """The local-update operators compiled for the host (operator-level tests only)."""
+    global _hostops
+    if _hostops is None:
+        H = C.CDLL(HOSTOPS_PATH)
+        H.tasi_host_fd_tri.restype = C.c_float
+        H.tasi_host_fd_tri.argtypes = [C.c_float] * 4
+        H.tasi_host_mfd_tri.restype = C.c_float
+        H.tasi_host_mfd_tri.argtypes = [C.c_float] * 3
+        H.tasi_host_dfm_stencil.restype = C.c_float
+        H.tasi_host_dfm_stencil.argtypes = [C.c_float] * 4
+        H.tasi_host_update.restype = C.c_float
+        H.tasi_host_update.argtypes = [C.c_int, _f32p, _f32p]
+        H.tasi_host_fd_tri_n.argtypes = [_f32p] * 5 + [C.c_long]
+        H.tasi_host_mfd_tri_n.argtypes = [_f32p] * 4 + [C.c_long]
+        H.tasi_host_dfm_stencil_n.argtypes = [_f32p] * 5 + [C.c_long]
+        _hostops = H
+    return _hostops

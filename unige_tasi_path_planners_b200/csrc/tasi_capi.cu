@@ -1,0 +1,579 @@
+// C ABI of the B200 cost-propagation core (declared in include/tasi_gpu.h).
+//
+// Host side of the solver: owns the device arrays of one planner (padded cost grid, padded value field, tile
+// states, work queue), mirrors the flag logic of ReplannerBase::step (ProjectToolkit/include/ReplannerBase.h:43-75)
+// and launches the kernels of tasi_solver.cuh. No CPU fallback: every entry point needs the CUDA device.
+#include <chrono>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "../../include/tasi_gpu.h"
+#include "tasi_solver.cuh"
+
+using namespace tasi;
+
+struct tasi_planner {
+    int kind = TASI_FD, level = 0, device = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    int num_sms = 0;
+
+    // the reference's flags (ReplannerBase.h:144-152)
+    bool initialize_graph = true, initialize_search = true, goal_set = false, new_goal = false, new_start = false;
+    int thr = 254;  // Graph.h:33
+    float heuristic_multiplier = 1.0f;
+    float start_x = 0, start_y = 0, goal_x = 0, goal_y = 0;
+    bool have_goal_elem = false;
+    int64_t goal_ex = -1, goal_ey = -1;  // goal element, global coordinates
+    uint64_t num_nodes_updated = 0, num_nodes_expanded = 0;
+
+    // geometry
+    int W = 0, rows = 0;  // stored cell columns / rows (band: includes the extra rows of open sides)
+    int EX = 0, EY = 0, TX = 0, TY = 0;
+    int64_t global_row0 = 0;
+    bool open_top = false, open_bottom = false;
+
+    // device memory
+    float *g_base = nullptr;
+    uint8_t *c_base = nullptr;
+    int64_t gpitch = 0, cpitch = 0, g_rows = 0;
+    int *state = nullptr, *queue = nullptr;
+    uint8_t *seed = nullptr;
+    DevCtl *ctl = nullptr;
+    float *stage = nullptr;  // 2 x EY receive rows (band mode)
+    uint8_t *patch_buf = nullptr, *chg_buf = nullptr;
+    size_t patch_cap = 0;
+    unsigned qsize = 0;
+    int n_tiles_alloc = 0;
+
+    // pending replan seeds
+    bool patch_pending = false;
+    uint64_t last_seed_count = 0;
+
+    int solver_blocks = 0;
+    double timeout_s = 60.0;
+    tasi_stats stats{};
+    std::string err;
+};
+
+namespace {
+
+#define CU_TRY(p, call)                                                                              \
+    do {                                                                                             \
+        cudaError_t e__ = (call);                                                                    \
+        if (e__ != cudaSuccess) {                                                                    \
+            (p)->err = std::string(#call) + ": " + cudaGetErrorString(e__);                          \
+            return TASI_ERR_CUDA;                                                                    \
+        }                                                                                            \
+    } while (0)
+
+inline bool node_based(const tasi_planner *p) { return p->kind != TASI_DFM; }
+
+inline float *g_origin(const tasi_planner *p) { return p->g_base + p->gpitch + GMARGIN; }
+inline uint8_t *c_origin(const tasi_planner *p) { return p->c_base + p->cpitch + GMARGIN; }
+
+GridDesc make_desc(const tasi_planner *p) {
+    GridDesc d;
+    d.g = g_origin(p);
+    d.gpitch = p->gpitch;
+    d.cost = c_origin(p);
+    d.cpitch = p->cpitch;
+    d.EX = p->EX; d.EY = p->EY; d.TX = p->TX; d.TY = p->TY;
+    d.L = p->rows; d.W = p->W;
+    d.thr = p->thr;
+    int64_t px = p->have_goal_elem ? p->goal_ex - p->global_row0 : -1;
+    int64_t py = p->have_goal_elem ? p->goal_ey : -1;
+    if (px < 0 || px >= p->EX || py < 0 || py >= p->EY) { px = -1000000; py = -1000000; }
+    d.pin_x = (int) px; d.pin_y = (int) py;
+    d.state = p->state; d.queue = p->queue; d.qmask = p->qsize - 1;
+    d.seed = p->seed; d.ctl = p->ctl;
+    d.inval_tol = (p->kind == TASI_DFM) ? 1e-6f : 0.0f;
+    return d;
+}
+
+void free_grid(tasi_planner *p) {
+    cudaFree(p->g_base); cudaFree(p->c_base); cudaFree(p->state); cudaFree(p->queue); cudaFree(p->seed);
+    cudaFree(p->stage);
+    p->g_base = nullptr; p->c_base = nullptr; p->state = nullptr; p->queue = nullptr; p->seed = nullptr;
+    p->stage = nullptr;
+}
+
+typedef void (*solver_fn)(GridDesc);
+solver_fn pick_solver(int kind, int mode) {
+    switch (kind * 2 + mode) {
+        case TASI_FD * 2 + 0: return solver_kernel<TASI_KIND_FD, 0>;
+        case TASI_FD * 2 + 1: return solver_kernel<TASI_KIND_FD, 1>;
+        case TASI_DFM * 2 + 0: return solver_kernel<TASI_KIND_DFM, 0>;
+        case TASI_DFM * 2 + 1: return solver_kernel<TASI_KIND_DFM, 1>;
+        case TASI_MFD * 2 + 0: return solver_kernel<TASI_KIND_MFD, 0>;
+        default: return solver_kernel<TASI_KIND_MFD, 1>;
+    }
+}
+
+// (Re)allocate the device arrays for a map of `rows` x `W` cells. Margins: cost bytes 255, values INF.
+int alloc_grid(tasi_planner *p, int W, int rows) {
+    int EX, EY;
+    if (node_based(p)) { EX = rows + 1 - (p->open_top ? 1 : 0) - (p->open_bottom ? 1 : 0); EY = W + 1; }
+    else { EX = rows; EY = W; }
+    if (EX <= 0 || EY <= 0) { p->err = "map too small for this band configuration"; return TASI_ERR_ARG; }
+    const bool same = p->g_base && p->W == W && p->rows == rows && p->EX == EX;
+    p->W = W; p->rows = rows; p->EX = EX; p->EY = EY;
+    if (same) return TASI_OK;
+    free_grid(p);
+    p->TX = (EX + TS - 1) / TS; p->TY = (EY + TS - 1) / TS;
+    p->gpitch = (int64_t) p->TY * TS + 2 * GMARGIN;
+    p->cpitch = (int64_t) p->TY * TS + 2 * GMARGIN;
+    p->g_rows = (int64_t) p->TX * TS + 2;
+    const int nt = p->TX * p->TY;
+    int dev_blocks = 0;
+    CU_TRY(p, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&dev_blocks, pick_solver(p->kind, 0), NTHREADS, 0));
+    int dev_blocks1 = 0;
+    CU_TRY(p, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&dev_blocks1, pick_solver(p->kind, 1), NTHREADS, 0));
+    if (dev_blocks1 < dev_blocks) dev_blocks = dev_blocks1;
+    if (dev_blocks < 1) { p->err = "solver kernel does not fit on an SM"; return TASI_ERR_CUDA; }
+    int blocks = dev_blocks * p->num_sms;
+    if (const char *e = getenv("TASI_BLOCKS_PER_SM")) {
+        int v = atoi(e);
+        if (v >= 1 && v <= dev_blocks) blocks = v * p->num_sms;
+    }
+    if (blocks > nt) blocks = nt;
+    p->solver_blocks = blocks;
+    unsigned q = 1;
+    while (q < (unsigned) std::max(nt, blocks) + 1u) q <<= 1;
+    p->qsize = q;
+    CU_TRY(p, cudaMalloc(&p->g_base, sizeof(float) * p->gpitch * p->g_rows));
+    CU_TRY(p, cudaMalloc(&p->c_base, (size_t) p->cpitch * p->g_rows));
+    CU_TRY(p, cudaMalloc(&p->state, sizeof(int) * nt));
+    CU_TRY(p, cudaMalloc(&p->queue, sizeof(int) * q));
+    CU_TRY(p, cudaMalloc(&p->seed, nt));
+    CU_TRY(p, cudaMalloc(&p->stage, sizeof(float) * 2 * (size_t) EY));
+    CU_TRY(p, cudaMemsetAsync(p->c_base, 255, (size_t) p->cpitch * p->g_rows, p->stream));
+    CU_TRY(p, cudaMemsetAsync(p->state, 0, sizeof(int) * nt, p->stream));
+    CU_TRY(p, cudaMemsetAsync(p->queue, 0, sizeof(int) * q, p->stream));
+    CU_TRY(p, cudaMemsetAsync(p->seed, 0, nt, p->stream));
+    p->n_tiles_alloc = nt;
+    p->initialize_search = true;  // a new geometry invalidates any previous field
+    p->patch_pending = false;
+    return TASI_OK;
+}
+
+inline double now_ms() {
+    return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
+int read_ctl(tasi_planner *p, DevCtl *h) {
+    CU_TRY(p, cudaMemcpyAsync(h, p->ctl, sizeof(DevCtl), cudaMemcpyDeviceToHost, p->stream));
+    CU_TRY(p, cudaStreamSynchronize(p->stream));
+    return TASI_OK;
+}
+
+// Queue the flagged tiles and run the persistent solver in `mode` until the queue drains.
+// Adds the launch's counters to p->stats; *ms = CUDA-event time of the three launches.
+int run_solver(tasi_planner *p, int mode, float *ms) {
+    GridDesc d = make_desc(p);
+    DevCtl z;
+    memset(&z, 0, sizeof z);
+    z.timeout_ns = (unsigned long long) (p->timeout_s * 1e9);
+    // reset queue tickets + per-launch counters, keep the patch bookkeeping
+    CU_TRY(p, cudaMemcpyAsync(p->ctl, &z, offsetof(DevCtl, n_changed), cudaMemcpyHostToDevice, p->stream));
+    CU_TRY(p, cudaEventRecord(p->ev0, p->stream));
+    const int nt = p->TX * p->TY;
+    enqueue_seeds_kernel<<<std::min((nt + 255) / 256, 1024), 256, 0, p->stream>>>(d);
+    arm_solver_kernel<<<1, 1, 0, p->stream>>>(d);
+    pick_solver(p->kind, mode)<<<p->solver_blocks, NTHREADS, 0, p->stream>>>(d);
+    CU_TRY(p, cudaGetLastError());
+    CU_TRY(p, cudaEventRecord(p->ev1, p->stream));
+    DevCtl h;
+    int rc = read_ctl(p, &h);
+    if (rc != TASI_OK) return rc;
+    CU_TRY(p, cudaEventElapsedTime(ms, p->ev0, p->ev1));
+    p->stats.solver_launches += 3;
+    p->stats.queue_pushes += h.pushes;
+    if (mode == 0) {
+        p->stats.tile_visits += h.visits;
+        p->stats.tile_rounds += h.rounds;
+        p->stats.elem_lowered += h.lowered;
+    } else {
+        p->stats.inval_visits += h.visits;
+        p->stats.elem_invalidated += h.invalidated;
+    }
+    if (h.error) {
+        p->err = "solver watchdog fired (work queue stalled)";
+        // leave the queue/state arrays clean for the next attempt
+        cudaMemsetAsync(p->state, 0, sizeof(int) * nt, p->stream);
+        cudaMemsetAsync(p->queue, 0, sizeof(int) * p->qsize, p->stream);
+        p->initialize_search = true;
+        return TASI_ERR_TIMEOUT;
+    }
+    return TASI_OK;
+}
+
+// init(): whole field INF, goal 0, goal tile flagged (FieldDPlanner_impl.h:15-21 and siblings).
+int init_field(tasi_planner *p) {
+    GridDesc d = make_desc(p);
+    const int nt = p->TX * p->TY;
+    CU_TRY(p, cudaMemsetAsync(p->seed, 0, nt, p->stream));
+    CU_TRY(p, cudaMemsetAsync(p->state, 0, sizeof(int) * nt, p->stream));
+    const int64_t n4 = p->gpitch * p->g_rows / 4;
+    fill_inf_kernel<<<p->num_sms * 8, 256, 0, p->stream>>>((float4 *) p->g_base, n4);
+    seed_goal_kernel<<<1, 1, 0, p->stream>>>(d);
+    CU_TRY(p, cudaGetLastError());
+    // patch bookkeeping restarts: the first plan reads the patched grid (ReplannerBase.h:52)
+    CU_TRY(p, cudaMemsetAsync(&p->ctl->n_changed, 0, sizeof(DevCtl) - offsetof(DevCtl, n_changed), p->stream));
+    p->patch_pending = false;
+    p->last_seed_count = 0;
+    p->stats.solver_launches += 2;
+    return TASI_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int tasi_create(int kind, int level, int device, tasi_planner **out) {
+    if (!out) return TASI_ERR_ARG;
+    *out = nullptr;
+    if (kind < TASI_FD || kind > TASI_MFD || level < 0 || level > (kind == TASI_MFD ? 2 : 1)) return TASI_ERR_ARG;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0 || device < 0 || device >= ndev) return TASI_ERR_CUDA;
+    tasi_planner *p = new (std::nothrow) tasi_planner();
+    if (!p) return TASI_ERR_ARG;
+    p->kind = kind; p->level = level; p->device = device;
+    if (cudaSetDevice(device) != cudaSuccess) { delete p; return TASI_ERR_CUDA; }
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) { delete p; return TASI_ERR_CUDA; }
+    p->num_sms = prop.multiProcessorCount;
+    if (cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreate(&p->ev0) != cudaSuccess || cudaEventCreate(&p->ev1) != cudaSuccess ||
+        cudaMalloc(&p->ctl, sizeof(DevCtl)) != cudaSuccess ||
+        cudaMemset(p->ctl, 0, sizeof(DevCtl)) != cudaSuccess) {
+        tasi_destroy(p);
+        return TASI_ERR_CUDA;
+    }
+    if (const char *e = getenv("TASI_TIMEOUT_S")) {
+        double v = atof(e);
+        if (v > 0) p->timeout_s = v;
+    }
+    *out = p;
+    return TASI_OK;
+}
+
+int tasi_destroy(tasi_planner *p) {
+    if (!p) return TASI_OK;
+    cudaSetDevice(p->device);
+    if (p->stream) cudaStreamSynchronize(p->stream);
+    free_grid(p);
+    cudaFree(p->ctl); cudaFree(p->patch_buf); cudaFree(p->chg_buf);
+    if (p->ev0) cudaEventDestroy(p->ev0);
+    if (p->ev1) cudaEventDestroy(p->ev1);
+    if (p->stream) cudaStreamDestroy(p->stream);
+    delete p;
+    return TASI_OK;
+}
+
+int tasi_reset(tasi_planner *p) {
+    if (!p) return TASI_ERR_ARG;
+    p->initialize_search = true;
+    return TASI_OK;
+}
+
+int tasi_set_occupancy_threshold(tasi_planner *p, float t) {
+    if (!p) return TASI_ERR_ARG;
+    p->thr = (int) (unsigned char) (t * 255.0f);  // Graph.cpp:18-20 (member is an unsigned char)
+    return TASI_OK;
+}
+
+int tasi_set_heuristic_multiplier(tasi_planner *p, float mult) {
+    if (!p) return TASI_ERR_ARG;
+    p->heuristic_multiplier = mult;
+    return TASI_OK;
+}
+
+static int set_map_common(tasi_planner *p, const uint8_t *src, int width, int length, int64_t pitch,
+                          cudaMemcpyKind kind) {
+    if (!p || !src || width <= 0 || length <= 0 || pitch < width) return TASI_ERR_ARG;
+    CU_TRY(p, cudaSetDevice(p->device));
+    int rc = alloc_grid(p, width, length);
+    if (rc != TASI_OK) return rc;
+    // band with an open top: the first stored row is the cell row above the first owned node row
+    const int dst_row0 = (node_based(p) && p->open_top) ? -1 : 0;
+    CU_TRY(p, cudaMemcpy2DAsync(c_origin(p) + (int64_t) dst_row0 * p->cpitch, p->cpitch, src, pitch, width, length,
+                                kind, p->stream));
+    CU_TRY(p, cudaStreamSynchronize(p->stream));  // the host pointer is not retained
+    p->initialize_graph = false;
+    return TASI_OK;
+}
+
+int tasi_set_map(tasi_planner *p, const uint8_t *host_map, int width, int length) {
+    return set_map_common(p, host_map, width, length, width, cudaMemcpyHostToDevice);
+}
+
+int tasi_set_map_device(tasi_planner *p, const uint8_t *dev_map, int width, int length, int64_t pitch) {
+    return set_map_common(p, dev_map, width, length, pitch, cudaMemcpyDeviceToDevice);
+}
+
+int tasi_synth_map(tasi_planner *p, uint64_t seed, int width, int length, int64_t row0, int p_obs, int sx, int sy,
+                   int gx, int gy) {
+    if (!p || width <= 0 || length <= 0) return TASI_ERR_ARG;
+    CU_TRY(p, cudaSetDevice(p->device));
+    int rc = alloc_grid(p, width, length);
+    if (rc != TASI_OK) return rc;
+    const int dst_row0 = (node_based(p) && p->open_top) ? -1 : 0;
+    synth_map_kernel<<<p->num_sms * 8, 256, 0, p->stream>>>(c_origin(p), p->cpitch, length, width, row0, dst_row0, seed,
+                                                           p_obs, sx, sy, gx, gy);
+    CU_TRY(p, cudaGetLastError());
+    CU_TRY(p, cudaStreamSynchronize(p->stream));
+    p->initialize_graph = false;
+    return TASI_OK;
+}
+
+int tasi_read_map(tasi_planner *p, uint8_t *host_out) {
+    if (!p || !host_out || p->initialize_graph) return TASI_ERR_ARG;
+    CU_TRY(p, cudaSetDevice(p->device));
+    const int dst_row0 = (node_based(p) && p->open_top) ? -1 : 0;
+    CU_TRY(p, cudaMemcpy2DAsync(host_out, p->W, c_origin(p) + (int64_t) dst_row0 * p->cpitch, p->cpitch, p->W, p->rows,
+                                cudaMemcpyDeviceToHost, p->stream));
+    CU_TRY(p, cudaStreamSynchronize(p->stream));
+    return TASI_OK;
+}
+
+int tasi_patch_map(tasi_planner *p, const uint8_t *host_patch, int x, int y, int w, int h, uint64_t *n_changed) {
+    if (!p || !host_patch || p->initialize_graph) return TASI_ERR_ARG;
+    if (x < 0 || y < 0 || w <= 0 || h <= 0 || (int64_t) x + h > p->rows || (int64_t) y + w > p->W) {
+        p->err = "patch outside the map";  // the reference asserts (Graph.cpp:38-41)
+        return TASI_ERR_ARG;
+    }
+    if (p->open_top || p->open_bottom) { p->err = "patch_map is not supported on a band"; return TASI_ERR_STATE; }
+    CU_TRY(p, cudaSetDevice(p->device));
+    const size_t n = (size_t) w * h;
+    if (n > p->patch_cap) {
+        cudaFree(p->patch_buf); cudaFree(p->chg_buf);
+        p->patch_buf = p->chg_buf = nullptr; p->patch_cap = 0;
+        CU_TRY(p, cudaMalloc(&p->patch_buf, n));
+        CU_TRY(p, cudaMalloc(&p->chg_buf, n));
+        p->patch_cap = n;
+    }
+    CU_TRY(p, cudaMemcpyAsync(p->patch_buf, host_patch, n, cudaMemcpyHostToDevice, p->stream));
+    CU_TRY(p, cudaMemsetAsync(&p->ctl->n_changed, 0, sizeof(unsigned long long), p->stream));
+    GridDesc d = make_desc(p);
+    const int blocks = (int) std::min<size_t>((n + 255) / 256, (size_t) p->num_sms * 16);
+    patch_apply_kernel<<<blocks, 256, 0, p->stream>>>(d, p->patch_buf, p->chg_buf, x, y, w, h);
+    switch (p->kind) {
+        case TASI_FD: patch_seed_kernel<TASI_KIND_FD><<<blocks, 256, 0, p->stream>>>(d, p->chg_buf, x, y, w, h); break;
+        case TASI_DFM: patch_seed_kernel<TASI_KIND_DFM><<<blocks, 256, 0, p->stream>>>(d, p->chg_buf, x, y, w, h); break;
+        default: patch_seed_kernel<TASI_KIND_MFD><<<blocks, 256, 0, p->stream>>>(d, p->chg_buf, x, y, w, h); break;
+    }
+    CU_TRY(p, cudaGetLastError());
+    DevCtl hc;
+    int rc = read_ctl(p, &hc);
+    if (rc != TASI_OK) return rc;
+    if (n_changed) *n_changed = hc.n_changed;
+    p->patch_pending = true;
+    return TASI_OK;
+}
+
+static void round_elem(float x, float y, int64_t *ex, int64_t *ey) {
+    *ex = (int64_t) roundf(x);  // Node(Position) / Cell(Position): Node.cpp:14-17, Cell.cpp:20-21
+    *ey = (int64_t) roundf(y);
+}
+
+int tasi_set_start(tasi_planner *p, float x, float y) {
+    if (!p) return TASI_ERR_ARG;
+    p->start_x = x; p->start_y = y;
+    p->new_start = true;
+    return TASI_OK;
+}
+
+int tasi_set_goal(tasi_planner *p, float x, float y) {
+    if (!p) return TASI_ERR_ARG;
+    int64_t ex, ey;
+    round_elem(x, y, &ex, &ey);
+    p->new_goal = !p->have_goal_elem || ex != p->goal_ex || ey != p->goal_ey;  // ReplannerBase.h:99-108
+    p->goal_x = x; p->goal_y = y; p->goal_ex = ex; p->goal_ey = ey;
+    p->have_goal_elem = true;
+    p->goal_set = true;
+    return TASI_OK;
+}
+
+int tasi_step(tasi_planner *p, float *u_ms, float *p_ms, uint64_t *n_updated, uint64_t *n_expanded) {
+    if (!p) return TASI_ERR_ARG;
+    if (p->initialize_graph) return TASI_LOOP_FAILURE_NO_GRAPH;  // ReplannerBase.h:44
+    if (!p->goal_set) return TASI_LOOP_FAILURE_NO_GOAL;         // ReplannerBase.h:45
+    CU_TRY(p, cudaSetDevice(p->device));
+    const uint64_t nt = (uint64_t) p->TX * p->TY;
+    memset(&p->stats, 0, sizeof p->stats);
+    p->stats.tiles = nt;
+    p->stats.solver_blocks = p->solver_blocks;
+    int rc;
+    float ms = 0;
+
+    double t0 = now_ms();
+    if (p->initialize_search || p->new_goal) {  // ReplannerBase.h:48-55
+        p->num_nodes_updated = 0;
+        p->num_nodes_expanded = 0;
+        CU_TRY(p, cudaEventRecord(p->ev0, p->stream));
+        rc = init_field(p);
+        if (rc != TASI_OK) return rc;
+        CU_TRY(p, cudaEventRecord(p->ev1, p->stream));
+        CU_TRY(p, cudaStreamSynchronize(p->stream));
+        CU_TRY(p, cudaEventElapsedTime(&ms, p->ev0, p->ev1));
+        p->stats.kernel_ms_init = ms;
+    } else if (p->new_start) {  // ReplannerBase.h:56-59 -> update()
+        p->new_start = false;
+        if (p->patch_pending) {
+            DevCtl hc;
+            rc = read_ctl(p, &hc);
+            if (rc != TASI_OK) return rc;
+            p->last_seed_count = hc.n_seed_elems;
+            // phase 1 of the repair: raised costs may have left values without support
+            if (hc.n_raised > 0) {
+                rc = run_solver(p, 1, &ms);
+                if (rc != TASI_OK) return rc;
+                p->stats.kernel_ms_inval = ms;
+            }
+            CU_TRY(p, cudaMemsetAsync(&p->ctl->n_changed, 0, sizeof(DevCtl) - offsetof(DevCtl, n_changed), p->stream));
+            p->patch_pending = false;
+        }
+        // the reference keeps Graph::updated_cells_ until the next patch, so update() re-seeds (and
+        // re-counts) the same elements on every new start
+        p->num_nodes_updated = p->last_seed_count;
+        p->stats.seed_elems = p->last_seed_count;
+        CU_TRY(p, cudaStreamSynchronize(p->stream));
+    }
+    double t1 = now_ms();
+
+    if (p->new_goal || p->initialize_search || p->num_nodes_updated > 0) {  // ReplannerBase.h:64-69 -> plan()
+        rc = run_solver(p, 0, &ms);
+        if (rc != TASI_OK) return rc;
+        p->stats.kernel_ms_solve = ms;
+        p->num_nodes_expanded = p->stats.elem_lowered;
+    } else {
+        p->num_nodes_expanded = 0;
+    }
+    p->new_goal = p->initialize_search = false;
+    double t2 = now_ms();
+
+    if (u_ms) *u_ms = (float) (t1 - t0);
+    if (p_ms) *p_ms = (float) (t2 - t1);
+    if (n_updated) *n_updated = p->num_nodes_updated;
+    if (n_expanded) *n_expanded = p->num_nodes_expanded;
+    return TASI_OK;
+}
+
+int tasi_field_dims(tasi_planner *p, int *ex, int *ey) {
+    if (!p || p->initialize_graph) return TASI_ERR_ARG;
+    if (ex) *ex = p->EX;
+    if (ey) *ey = p->EY;
+    return TASI_OK;
+}
+
+int tasi_read_window(tasi_planner *p, int x0, int y0, int nx, int ny, float *host_out) {
+    if (!p || !host_out || nx <= 0 || ny <= 0 || p->initialize_graph) return TASI_ERR_ARG;
+    CU_TRY(p, cudaSetDevice(p->device));
+    const int xa = std::max(x0, 0), xb = std::min(x0 + nx, p->EX);
+    const int ya = std::max(y0, 0), yb = std::min(y0 + ny, p->EY);
+    const bool clipped = xa != x0 || ya != y0 || xb != x0 + nx || yb != y0 + ny;
+    if (clipped)
+        for (int64_t i = 0; i < (int64_t) nx * ny; ++i) host_out[i] = INFINITY;
+    if (xa < xb && ya < yb) {
+        CU_TRY(p, cudaMemcpy2DAsync(host_out + (int64_t) (xa - x0) * ny + (ya - y0), sizeof(float) * ny,
+                                    g_origin(p) + (int64_t) xa * p->gpitch + ya, sizeof(float) * p->gpitch,
+                                    sizeof(float) * (yb - ya), xb - xa, cudaMemcpyDeviceToHost, p->stream));
+        CU_TRY(p, cudaStreamSynchronize(p->stream));
+    }
+    return TASI_OK;
+}
+
+int tasi_read_field(tasi_planner *p, float *host_out) {
+    if (!p || p->initialize_graph) return TASI_ERR_ARG;
+    return tasi_read_window(p, 0, 0, p->EX, p->EY, host_out);
+}
+
+int tasi_field_device(tasi_planner *p, float **dev_ptr, int64_t *pitch_elems) {
+    if (!p || !p->g_base) return TASI_ERR_ARG;
+    if (dev_ptr) *dev_ptr = g_origin(p);
+    if (pitch_elems) *pitch_elems = p->gpitch;
+    return TASI_OK;
+}
+
+int tasi_cost_device(tasi_planner *p, uint8_t **dev_ptr, int64_t *pitch_bytes) {
+    if (!p || !p->c_base) return TASI_ERR_ARG;
+    if (dev_ptr) *dev_ptr = c_origin(p);
+    if (pitch_bytes) *pitch_bytes = p->cpitch;
+    return TASI_OK;
+}
+
+int tasi_get_stats(tasi_planner *p, tasi_stats *out) {
+    if (!p || !out) return TASI_ERR_ARG;
+    *out = p->stats;
+    return TASI_OK;
+}
+
+const char *tasi_last_error(tasi_planner *p) { return p ? p->err.c_str() : "null planner"; }
+
+// ---- row bands -------------------------------------------------------------------------------------------------
+int tasi_band_config(tasi_planner *p, int64_t global_row0, int open_top, int open_bottom) {
+    if (!p) return TASI_ERR_ARG;
+    if (!p->initialize_graph) { p->err = "band_config must precede set_map"; return TASI_ERR_STATE; }
+    p->global_row0 = global_row0;
+    p->open_top = open_top != 0;
+    p->open_bottom = open_bottom != 0;
+    return TASI_OK;
+}
+
+int tasi_band_rows(tasi_planner *p, int side, float **send_row, float **recv_stage, int64_t *count) {
+    if (!p || !p->g_base || side < 0 || side > 1) return TASI_ERR_ARG;
+    if (send_row) *send_row = g_origin(p) + (side == 0 ? 0 : (int64_t) (p->EX - 1) * p->gpitch);
+    if (recv_stage) *recv_stage = p->stage + (size_t) side * p->EY;
+    if (count) *count = p->EY;
+    return TASI_OK;
+}
+
+int tasi_band_import(tasi_planner *p, int side, uint64_t *n_lowered) {
+    if (!p || !p->g_base || side < 0 || side > 1) return TASI_ERR_ARG;
+    CU_TRY(p, cudaSetDevice(p->device));
+    CU_TRY(p, cudaMemsetAsync(&p->ctl->halo_lowered, 0, sizeof(unsigned long long), p->stream));
+    GridDesc d = make_desc(p);
+    band_import_kernel<<<(p->EY + 255) / 256, 256, 0, p->stream>>>(d, p->stage + (size_t) side * p->EY,
+                                                                 side == 0 ? -1 : p->EX, side == 0 ? 0 : p->TX - 1);
+    CU_TRY(p, cudaGetLastError());
+    DevCtl hc;
+    int rc = read_ctl(p, &hc);
+    if (rc != TASI_OK) return rc;
+    if (n_lowered) *n_lowered = hc.halo_lowered;
+    return TASI_OK;
+}
+
+int tasi_band_begin(tasi_planner *p) {
+    if (!p) return TASI_ERR_ARG;
+    if (p->initialize_graph) return TASI_LOOP_FAILURE_NO_GRAPH;
+    if (!p->goal_set) return TASI_LOOP_FAILURE_NO_GOAL;
+    CU_TRY(p, cudaSetDevice(p->device));
+    memset(&p->stats, 0, sizeof p->stats);
+    p->stats.tiles = (uint64_t) p->TX * p->TY;
+    p->stats.solver_blocks = p->solver_blocks;
+    int rc = init_field(p);
+    if (rc != TASI_OK) return rc;
+    CU_TRY(p, cudaStreamSynchronize(p->stream));
+    p->new_goal = p->initialize_search = false;
+    return TASI_OK;
+}
+
+int tasi_band_solve(tasi_planner *p, uint64_t *n_tile_visits) {
+    if (!p || !p->g_base) return TASI_ERR_ARG;
+    CU_TRY(p, cudaSetDevice(p->device));
+    const uint64_t before = p->stats.tile_visits;
+    float ms = 0;
+    int rc = run_solver(p, 0, &ms);
+    if (rc != TASI_OK) return rc;
+    p->stats.kernel_ms_solve += ms;
+    if (n_tile_visits) *n_tile_visits = p->stats.tile_visits - before;
+    return TASI_OK;
+}
+
+}  // extern "C"

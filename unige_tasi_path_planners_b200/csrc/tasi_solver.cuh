@@ -1,0 +1,438 @@
+// Tiled active-list solver for the cost-to-go field of FD*, MS-DFM and MFD* (sm_100a).
+//
+// Replaces the reference's open-list expansion — plan() in FieldDStar/FieldDPlanner_impl.h:23-116,
+// DynamicFastMarching/DynamicFastMarching_impl.h:13-104, ShiftedGridFastMarching/ShiftedGridPlanner_impl.h:17-170
+// with its PriorityQueue (ProjectToolkit/include/PriorityQueue.h) and ExpandedMap
+// (ProjectToolkit/include/ExpandedMap.h) — by a label-correcting solve to the same fixed point:
+//
+//   * the element grid is cut into 32x32 tiles; a persistent grid of CTAs pulls active tiles from a device
+//     ticket queue, stages the tile (+1 halo ring) and the cell costs around it in shared memory, and relaxes it
+//     to tile-local convergence with four concurrent directional Gauss-Seidel sweeps (one warp each:
+//     rows down / rows up / columns right / columns left), accepting only decreases;
+//   * a tile whose border changed activates the neighbour tiles that read that border;
+//   * the same machinery run in "invalidate" mode is phase 1 of a replan: an element whose stored value is
+//     no longer supported by its neighbours under the new costs is reset to INF (what the reference's
+//     under-consistent branch does lazily, FieldDPlanner_impl.h:98-112), then phase 2 re-relaxes.
+//
+// Tile states: 0 idle, DIRTY queued, RUN being processed, RUN|DIRTY halo changed while processing (the
+// same CTA reloads and continues). A tile is in the queue at most once, so a ring of >= max(tiles, CTAs)
+// slots can never overflow; poppers take tickets and wait for their slot, `pending` (queued + running
+// tiles) reaching 0 ends the kernel. A wall-clock watchdog turns any would-be hang into an error code.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "tasi_update.cuh"
+
+namespace tasi {
+
+constexpr int TS = 32;         // tile side (elements)
+constexpr int GP = 35;         // shared-memory pitch of the value tile (34 used; odd => row and column
+                               // sweeps are both bank-conflict free)
+constexpr int CP = 35;         // shared-memory pitch of the cost tile (33 used for node planners)
+constexpr int NTHREADS = 128;  // 4 warps = 4 sweep directions
+constexpr int ST_DIRTY = 1;
+constexpr int ST_RUN = 2;
+constexpr int GMARGIN = 32;    // columns of margin left of element/cell column 0 (keeps rows 128B aligned)
+
+struct DevCtl {
+    unsigned long long head, tail;  // ticket counters of the work queue
+    int pending;                    // tiles queued or running
+    int done;                       // set when pending drops to 0 (or on error)
+    int error;                      // 1 = watchdog fired
+    int pad0;
+    unsigned long long visits, rounds, lowered, pushes, invalidated;
+    unsigned long long timeout_ns;
+    // patch bookkeeping
+    unsigned long long n_changed, n_raised, n_lowered_cells, n_seed_elems;
+    unsigned long long halo_lowered;
+};
+
+struct GridDesc {
+    float *g;              // element (0,0); rows -1..TX*32 and GMARGIN columns either side exist
+    int64_t gpitch;        // elements per row
+    uint8_t *cost;         // cell (0,0); rows -1..TX*32 and margins exist, margin bytes are 255
+    int64_t cpitch;        // bytes per row
+    int EX, EY;            // element-grid extents owned by this planner (band)
+    int TX, TY;            // tiles
+    int L, W;              // cell rows / columns stored (band-local)
+    int thr;               // occupancy threshold byte: cost >= thr is an obstacle (Graph.cpp:262-268)
+    int pin_x, pin_y;      // goal element in local coordinates (outside the grid = none)
+    int *state;            // TX*TY tile states
+    int *queue;            // ring of tile id + 1, 0 = empty
+    unsigned qmask;        // ring size - 1
+    uint8_t *seed;         // TX*TY: tiles to enqueue before the next solver launch
+    DevCtl *ctl;
+    float inval_tol;       // relative slack of the invalidate test (0 for FD*/MFD*)
+};
+
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+
+// ---- work queue (called by one thread per CTA) ------------------------------------------------------------
+__device__ __forceinline__ void q_fail(const GridDesc &d) {
+    atomicExch(&d.ctl->error, 1);
+    atomicExch(&d.ctl->done, 1);
+}
+
+__device__ inline void q_push(const GridDesc &d, int tile) {
+    atomicAdd(&d.ctl->pending, 1);
+    unsigned long long t = atomicAdd(&d.ctl->tail, 1ULL);
+    int *slot = &d.queue[(unsigned) t & d.qmask];
+    unsigned long long t0 = 0;
+    while (atomicCAS(slot, 0, tile + 1) != 0) {  // slot still held by a slow popper of the previous lap
+        if (t0 == 0) t0 = globaltimer_ns();
+        else if (globaltimer_ns() - t0 > d.ctl->timeout_ns) { q_fail(d); return; }
+        __nanosleep(64);
+    }
+}
+
+__device__ inline int q_pop(const GridDesc &d) {
+    unsigned long long t = atomicAdd(&d.ctl->head, 1ULL);
+    volatile int *slot = &d.queue[(unsigned) t & d.qmask];
+    volatile int *done = &d.ctl->done;
+    unsigned long long t0 = 0;
+    unsigned ns = 32;
+    for (;;) {
+        int v = *slot;
+        if (v != 0) {
+            *slot = 0;
+            return v - 1;
+        }
+        if (*done) return -1;
+        if (t0 == 0) t0 = globaltimer_ns();
+        else if (globaltimer_ns() - t0 > d.ctl->timeout_ns) { q_fail(d); return -1; }
+        __nanosleep(ns);
+        if (ns < 1024) ns <<= 1;
+    }
+}
+
+__device__ __forceinline__ void activate(const GridDesc &d, int tile) {
+    int old = atomicOr(&d.state[tile], ST_DIRTY);
+    if (old == 0) {
+        q_push(d, tile);
+        atomicAdd(&d.ctl->pushes, 1ULL);
+    }
+}
+
+// ---- one directional sweep of a staged tile by one warp ------------------------------------------------------
+// dir 0: rows top->bottom (lane = column), 1: rows bottom->top, 2: columns left->right (lane = row),
+// 3: columns right->left. rlim/clim = number of owned rows/columns inside this tile (elements beyond the
+// grid are never written). MODE 0 relaxes (accept decreases), MODE 1 invalidates unsupported values.
+template <int KIND, int MODE>
+__device__ __forceinline__ int sweep_tile(float *sg, const float *sc, int dir, int lane, int rlim, int clim,
+                                          int pin_r, int pin_c, float tol) {
+    const float INF = __int_as_float(0x7f800000);
+    const bool rowmode = dir < 2;
+    const bool rev = dir & 1;
+    const int lim_line = rowmode ? rlim : clim;
+    const bool lane_ok = lane < (rowmode ? clim : rlim);
+    int cnt = 0;
+    for (int s = 0; s < TS; ++s) {
+        const int line = rev ? (TS - 1 - s) : s;
+        if (line < lim_line && lane_ok) {
+            const int r = rowmode ? line : lane;
+            const int c = rowmode ? lane : line;
+            volatile float *p = sg + (r + 1) * GP + (c + 1);
+            const float cur = *p;
+            Nbr8 nb;
+            nb.n = p[-GP]; nb.s = p[GP]; nb.w = p[-1]; nb.e = p[1];
+            nb.nw = p[-GP - 1]; nb.ne = p[-GP + 1]; nb.sw = p[GP - 1]; nb.se = p[GP + 1];
+            float v;
+            if (KIND == TASI_KIND_DFM) {
+                v = dfm_cell(nb, sc[r * CP + c]);
+            } else {
+                const float *q = sc + r * CP + c;  // sc[i][j] = cost of cell (x0-1+i, y0-1+j)
+                const float tl = q[0], tr = q[1], bl = q[CP], br = q[CP + 1];
+                v = (KIND == TASI_KIND_FD) ? fd_node(nb, tl, tr, bl, br) : mfd_node(nb, tl, tr, bl, br);
+            }
+            if (MODE == 0) {
+                if (v < cur) {
+                    // non-negative floats order like their bit patterns; concurrent sweeps never raise a value
+                    atomicMin((int *) (sg + (r + 1) * GP + (c + 1)), __float_as_int(v));
+                    ++cnt;
+                }
+            } else {
+                if (cur < INF && !(r == pin_r && c == pin_c) && v > cur + cur * tol) {
+                    *p = INF;
+                    ++cnt;
+                }
+            }
+        }
+        __syncwarp();
+    }
+    return cnt;
+}
+
+// ---- the persistent solver kernel ------------------------------------------------------------------------------
+// Border-change bits: which neighbour tiles read the cells that changed.
+constexpr int NB_N = 1, NB_S = 2, NB_W = 4, NB_E = 8, NB_NW = 16, NB_NE = 32, NB_SW = 64, NB_SE = 128;
+
+template <int KIND, int MODE>
+__global__ void __launch_bounds__(NTHREADS) solver_kernel(GridDesc d) {
+    __shared__ float sg[(TS + 2) * GP];   // values, rows/cols -1..32
+    __shared__ float sg0[TS * TS];        // interior as loaded (change detection at write-back)
+    __shared__ float sc[(TS + 1) * CP];   // cell costs as float, INF = obstacle
+    __shared__ int s_tile, s_mask, s_again;
+
+    const float INF = __int_as_float(0x7f800000);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    unsigned long long n_visits = 0, n_rounds = 0, n_changed = 0;
+
+    for (;;) {
+        if (tid == 0) {
+            int t = q_pop(d);
+            if (t >= 0) {
+                atomicExch(&d.state[t], ST_RUN);  // clears DIRTY: everything written before it was set is
+                __threadfence();                  // visible to the loads below
+            }
+            s_tile = t;
+            s_mask = 0;
+        }
+        __syncthreads();
+        const int tile = s_tile;
+        if (tile < 0) break;
+        const int tx = tile / d.TY, ty = tile - tx * d.TY;
+        const int x0 = tx * TS, y0 = ty * TS;
+        const int rlim = min(TS, d.EX - x0), clim = min(TS, d.EY - y0);
+        const int pin_r = d.pin_x - x0, pin_c = d.pin_y - y0;
+
+        // cell costs around the tile (immutable while the solver runs)
+        if (KIND == TASI_KIND_DFM) {
+            for (int i = tid; i < TS * TS; i += NTHREADS) {
+                const int r = i >> 5, c = i & 31;
+                const uint8_t b = __ldg(d.cost + (int64_t) (x0 + r) * d.cpitch + (y0 + c));
+                sc[r * CP + c] = (b >= d.thr) ? INF : (float) b;
+            }
+        } else {
+            for (int i = tid; i < (TS + 1) * (TS + 1); i += NTHREADS) {
+                const int r = i / (TS + 1), c = i - r * (TS + 1);
+                const uint8_t b = __ldg(d.cost + (int64_t) (x0 - 1 + r) * d.cpitch + (y0 - 1 + c));
+                sc[r * CP + c] = (b >= d.thr) ? INF : (float) b;
+            }
+        }
+
+        bool again;
+        do {
+            // stage values + halo ring; L1 is bypassed (other CTAs write these lines)
+            for (int i = tid; i < (TS + 2) * (TS + 2); i += NTHREADS) {
+                const int r = i / (TS + 2), c = i - r * (TS + 2);
+                const float v = __ldcg(d.g + (int64_t) (x0 - 1 + r) * d.gpitch + (y0 - 1 + c));
+                sg[r * GP + c] = v;
+                if (r >= 1 && r <= TS && c >= 1 && c <= TS) sg0[(r - 1) * TS + (c - 1)] = v;
+            }
+            __syncthreads();
+            ++n_visits;
+
+            for (;;) {
+                const int ch = sweep_tile<KIND, MODE>(sg, sc, warp, lane, rlim, clim, pin_r, pin_c, d.inval_tol);
+                n_changed += ch;
+                ++n_rounds;
+                if (!__syncthreads_or(ch)) break;
+            }
+
+            // write back what changed, note which borders moved
+            int m = 0;
+            for (int i = tid; i < TS * TS; i += NTHREADS) {
+                const int r = i >> 5, c = i & 31;
+                const float v = sg[(r + 1) * GP + (c + 1)];
+                if (v != sg0[i]) {
+                    d.g[(int64_t) (x0 + r) * d.gpitch + (y0 + c)] = v;
+                    if (r == 0) m |= NB_N | (c == 0 ? NB_NW : 0) | (c == TS - 1 ? NB_NE : 0);
+                    if (r == TS - 1) m |= NB_S | (c == 0 ? NB_SW : 0) | (c == TS - 1 ? NB_SE : 0);
+                    if (c == 0) m |= NB_W;
+                    if (c == TS - 1) m |= NB_E;
+                }
+            }
+            m = __reduce_or_sync(0xffffffffu, m);
+            if (lane == 0 && m) atomicOr(&s_mask, m);
+            __threadfence();
+            __syncthreads();
+
+            if (tid == 0) {
+                const int mk = s_mask;
+                s_mask = 0;
+                if (MODE == 1) d.seed[tile] = 1;  // phase 2 revisits every tile phase 1 looked at
+                const bool hn = tx > 0, hs = tx + 1 < d.TX, hw = ty > 0, he = ty + 1 < d.TY;
+                if ((mk & NB_N) && hn) activate(d, tile - d.TY);
+                if ((mk & NB_S) && hs) activate(d, tile + d.TY);
+                if ((mk & NB_W) && hw) activate(d, tile - 1);
+                if ((mk & NB_E) && he) activate(d, tile + 1);
+                if ((mk & NB_NW) && hn && hw) activate(d, tile - d.TY - 1);
+                if ((mk & NB_NE) && hn && he) activate(d, tile - d.TY + 1);
+                if ((mk & NB_SW) && hs && hw) activate(d, tile + d.TY - 1);
+                if ((mk & NB_SE) && hs && he) activate(d, tile + d.TY + 1);
+                // leave the tile, unless a neighbour changed our halo meanwhile
+                int old = atomicCAS(&d.state[tile], ST_RUN, 0);
+                if (old != ST_RUN) {
+                    atomicExch(&d.state[tile], ST_RUN);
+                    __threadfence();
+                    s_again = 1;
+                } else {
+                    s_again = 0;
+                }
+                if (*(volatile int *) &d.ctl->error) s_again = 0;
+            }
+            __syncthreads();
+            again = s_again != 0;
+        } while (again);
+
+        if (tid == 0) {
+            if (atomicSub(&d.ctl->pending, 1) == 1) {
+                __threadfence();
+                atomicExch(&d.ctl->done, 1);
+            }
+        }
+    }
+
+    // per-CTA counters -> global statistics
+    n_changed = __reduce_add_sync(0xffffffffu, (unsigned) n_changed);
+    if (lane == 0 && n_changed) atomicAdd(MODE == 0 ? &d.ctl->lowered : &d.ctl->invalidated, n_changed);
+    if (tid == 0) {
+        atomicAdd(&d.ctl->visits, n_visits);
+        atomicAdd(&d.ctl->rounds, n_rounds);
+    }
+}
+
+// ---- auxiliary kernels -----------------------------------------------------------------------------------------
+// Fill `n4` float4 (the whole padded value array, margins included) with INF.
+__global__ void fill_inf_kernel(float4 *p, int64_t n4) {
+    const float INF = __int_as_float(0x7f800000);
+    const float4 v = make_float4(INF, INF, INF, INF);
+    for (int64_t i = blockIdx.x * (int64_t) blockDim.x + threadIdx.x; i < n4; i += (int64_t) gridDim.x * blockDim.x)
+        p[i] = v;
+}
+
+// init() of the three planners (FieldDPlanner_impl.h:15-21, DynamicFastMarching_impl.h:6-11,
+// ShiftedGridPlanner_impl.h:9-15): goal value 0, its tile is the first active tile.
+__global__ void seed_goal_kernel(GridDesc d) {
+    if (d.pin_x >= 0 && d.pin_x < d.EX && d.pin_y >= 0 && d.pin_y < d.EY) {
+        d.g[(int64_t) d.pin_x * d.gpitch + d.pin_y] = 0.0f;
+        d.seed[(d.pin_x / TS) * d.TY + (d.pin_y / TS)] = 1;
+    }
+}
+
+// Move the tiles flagged in seed[] into the work queue (runs alone, before the solver).
+__global__ void enqueue_seeds_kernel(GridDesc d) {
+    const int n = d.TX * d.TY;
+    for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < n; t += gridDim.x * blockDim.x) {
+        if (d.seed[t]) {
+            d.seed[t] = 0;
+            if (atomicOr(&d.state[t], ST_DIRTY) == 0) {
+                atomicAdd(&d.ctl->pending, 1);
+                unsigned long long s = atomicAdd(&d.ctl->tail, 1ULL);
+                d.queue[(unsigned) s & d.qmask] = t + 1;
+                atomicAdd(&d.ctl->pushes, 1ULL);
+            }
+        }
+    }
+}
+
+// Nothing queued => the solver must see done == 1 or its CTAs would wait for work forever.
+__global__ void arm_solver_kernel(GridDesc d) {
+    d.ctl->done = (d.ctl->pending == 0) ? 1 : 0;
+}
+
+// Graph::update (ProjectToolkit/Graph.cpp:36-51) on the device cost grid: rows x..x+h-1, cols y..y+w-1 take
+// the patch bytes; chg[] records which cells changed and whether the traversal cost went up (2) or down (1).
+__global__ void patch_apply_kernel(GridDesc d, const uint8_t *patch, uint8_t *chg, int x, int y, int w, int h) {
+    const int64_t n = (int64_t) w * h;
+    unsigned long long c_all = 0, c_up = 0, c_dn = 0;
+    for (int64_t i = blockIdx.x * (int64_t) blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x) {
+        const int pi = (int) (i / w), pj = (int) (i - (int64_t) pi * w);
+        uint8_t *mv = d.cost + (int64_t) (x + pi) * d.cpitch + (y + pj);
+        const uint8_t ov = *mv, nv = patch[i];
+        uint8_t f = 0;
+        if (ov != nv) {
+            // effective traversal cost: bytes >= thr are all the same obstacle
+            const int oe = ov >= d.thr ? 256 : ov, ne = nv >= d.thr ? 256 : nv;
+            f = ne > oe ? 2 : (ne < oe ? 1 : 3);  // 3: byte changed, cost did not
+            *mv = nv;
+            ++c_all;
+            if (f == 2) ++c_up;
+            if (f == 1) ++c_dn;
+        }
+        chg[i] = f;
+    }
+    if (c_all) atomicAdd(&d.ctl->n_changed, c_all);
+    if (c_up) atomicAdd(&d.ctl->n_raised, c_up);
+    if (c_dn) atomicAdd(&d.ctl->n_lowered_cells, c_dn);
+}
+
+// update() of the planners: FD*/MFD* seed the 4 corner nodes of every changed cell
+// (FieldDPlanner_impl.h:127-136, ShiftedGridPlanner_impl.h:172-195), MS-DFM the changed cell itself
+// (DynamicFastMarching_impl.h:106-112). Counts the distinct seeded elements (num_nodes_updated) and flags
+// their tiles. Elements of the patch range: nodes (x..x+h, y..y+w), cells (x..x+h-1, y..y+w-1).
+template <int KIND>
+__global__ void patch_seed_kernel(GridDesc d, const uint8_t *chg, int x, int y, int w, int h) {
+    const int ew = (KIND == TASI_KIND_DFM) ? w : w + 1, eh = (KIND == TASI_KIND_DFM) ? h : h + 1;
+    const int64_t n = (int64_t) ew * eh;
+    unsigned long long cnt = 0;
+    for (int64_t i = blockIdx.x * (int64_t) blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x) {
+        const int ei = (int) (i / ew), ej = (int) (i - (int64_t) ei * ew);
+        bool hit;
+        if (KIND == TASI_KIND_DFM) {
+            hit = chg[(int64_t) ei * w + ej] != 0;
+        } else {
+            hit = false;
+            for (int di = -1; di <= 0; ++di)
+                for (int dj = -1; dj <= 0; ++dj) {
+                    const int ci = ei + di, cj = ej + dj;
+                    if (ci >= 0 && ci < h && cj >= 0 && cj < w && chg[(int64_t) ci * w + cj] != 0) hit = true;
+                }
+        }
+        if (hit) {
+            ++cnt;
+            const int gx = x + ei, gy = y + ej;
+            if (gx < d.EX && gy < d.EY) d.seed[(gx / TS) * d.TY + (gy / TS)] = 1;
+        }
+    }
+    if (cnt) atomicAdd(&d.ctl->n_seed_elems, cnt);
+}
+
+// Row-band sharding: merge a received boundary row into the halo row (`hrow` = -1 or EX) and flag the
+// tiles that read the elements that got lower.
+__global__ void band_import_kernel(GridDesc d, const float *stage, int hrow, int trow) {
+    unsigned long long cnt = 0;
+    for (int yy = blockIdx.x * blockDim.x + threadIdx.x; yy < d.EY; yy += gridDim.x * blockDim.x) {
+        float *hp = d.g + (int64_t) hrow * d.gpitch + yy;
+        const float nv = stage[yy];
+        if (nv < *hp) {
+            *hp = nv;
+            ++cnt;
+            const int ty = yy / TS;
+            d.seed[trow * d.TY + ty] = 1;
+            if ((yy & (TS - 1)) == 0 && ty > 0) d.seed[trow * d.TY + ty - 1] = 1;
+            if ((yy & (TS - 1)) == TS - 1 && ty + 1 < d.TY) d.seed[trow * d.TY + ty + 1] = 1;
+        }
+    }
+    if (cnt) atomicAdd(&d.ctl->halo_lowered, cnt);
+}
+
+// Deterministic synthetic traversability grid (same function as synth.py):
+// h = splitmix64(seed ^ (gx*W + gy)); obstacle (255) if h % 1000 < 10*p_obs else 1 + ((h >> 16) % 64);
+// 9x9 blocks of cost 1 around (sx,sy) and (gx,gy) (global cell coordinates, negative = none).
+__device__ __forceinline__ uint64_t splitmix64(uint64_t z) {
+    z += 0x9E3779B97F4A7C15ULL;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
+    return z ^ (z >> 31);
+}
+
+__global__ void synth_map_kernel(uint8_t *cost, int64_t cpitch, int rows, int W, int64_t row0, int dst_row0,
+                                 uint64_t seed, int p_obs, int sx, int sy, int gx, int gy) {
+    const int64_t n = (int64_t) rows * W;
+    for (int64_t i = blockIdx.x * (int64_t) blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x) {
+        const int r = (int) (i / W), c = (int) (i - (int64_t) r * W);
+        const int64_t x = row0 + r;
+        const uint64_t hsh = splitmix64(seed ^ ((uint64_t) x * (uint64_t) W + (uint64_t) c));
+        uint8_t v = (hsh % 1000ULL) < (uint64_t) (10 * p_obs) ? 255 : (uint8_t) (1 + ((hsh >> 16) % 64ULL));
+        if (sx >= 0 && x >= sx - 4 && x <= sx + 4 && c >= sy - 4 && c <= sy + 4) v = 1;
+        if (gx >= 0 && x >= gx - 4 && x <= gx + 4 && c >= gy - 4 && c <= gy + 4) v = 1;
+        cost[(int64_t) (dst_row0 + r) * cpitch + c] = v;
+    }
+}
+
+}  // namespace tasi

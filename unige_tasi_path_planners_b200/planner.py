@@ -1,0 +1,228 @@
+"""Python mirror of the reference's planner interface over the C ABI (include/tasi_gpu.h).
+
+Same method names, argument meaning and return codes as ReplannerBase
+(ProjectToolkit/include/ReplannerBase.h:39-123): reset, step, set_occupancy_threshold,
+set_heuristic_multiplier, set_map, patch_map(patch, x, y, w, h), set_start, set_goal, and the public fields
+u_time, p_time, num_nodes_updated, num_nodes_expanded. The three classes correspond to
+FieldDPlanner<O> (FieldDStar/FieldDPlanner.h), DFMPlanner<O> (DynamicFastMarching/DynamicFastMarching.h) and
+ShiftedGridPlanner<O> (ShiftedGridFastMarching/ShiftedGridPlanner.h).
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from ._lib import FD, DFM, MFD, LOOP_OK, LOOP_FAILURE_NO_GRAPH, LOOP_FAILURE_NO_GOAL  # noqa: F401
+
+
+class TasiError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("tasi error %d: %s" % (code, msg))
+        self.code = code
+
+
+class FieldView:
+    """What the path extractor reads after a step: the converged value of every element (g == rhs).
+
+    Stands where `const ExpandedMap<E,T>&` stands in the reference (get_expanded_map, ReplannerBase.h:117-119);
+    get_g / get_rhs / get_interp_rhs follow ExpandedMap_impl.h:65-97.
+    """
+
+    def __init__(self, planner):
+        self._p = planner
+
+    def window(self, x0, y0, nx, ny):
+        return self._p.read_window(x0, y0, nx, ny)
+
+    def get_g(self, x, y):
+        return float(self._p.read_window(int(x), int(y), 1, 1)[0, 0])
+
+    get_rhs = get_g
+
+    def get_interp_rhs(self, x, y):
+        """Node value seen by the extractor: the node's own rhs (node planners) or the mean of the 4 cells
+        around it (MS-DFM, ExpandedMap_impl.h:87-92)."""
+        if self._p.kind != DFM:
+            return self.get_g(x, y)
+        w = self._p.read_window(int(x) - 1, int(y) - 1, 2, 2)
+        return float((w[0, 0] + w[0, 1] + w[1, 0] + w[1, 1]) / np.float32(4.0))
+
+
+class GpuPlanner:
+    kind = FD
+    max_level = 1
+
+    def __init__(self, level=1, device=0):
+        if not (0 <= level <= self.max_level):
+            raise ValueError("optimisation level %d not defined for this planner" % level)
+        self._L = _lib.lib()
+        h = C.c_void_p()
+        rc = self._L.tasi_create(self.kind, level, device, C.byref(h))
+        if rc != _lib.OK:
+            raise TasiError(rc, "tasi_create failed (no CUDA device? there is no CPU fallback)")
+        self._h = h
+        self.level = level
+        self.device = device
+        self.u_time = 0.0
+        self.p_time = 0.0
+        self.num_nodes_updated = 0
+        self.num_nodes_expanded = 0
+        self.heuristic_multiplier = 1.0
+        self.width = self.length = 0
+
+    # -- lifetime ------------------------------------------------------------------------------------------
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.tasi_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc):
+        if rc < _lib.LOOP_FAILURE_NO_GOAL:
+            raise TasiError(rc, self._L.tasi_last_error(self._h).decode())
+        return rc
+
+    # -- the reference's public surface -------------------------------------------------------------------------
+    def reset(self):
+        self._check(self._L.tasi_reset(self._h))
+
+    def set_occupancy_threshold(self, threshold):
+        self._check(self._L.tasi_set_occupancy_threshold(self._h, threshold))
+
+    def set_heuristic_multiplier(self, mult):
+        self.heuristic_multiplier = mult
+        self._check(self._L.tasi_set_heuristic_multiplier(self._h, mult))
+
+    def set_map(self, new_map, w=None, h=None):
+        """new_map: uint8 array of h rows by w columns (numpy), or a CUDA torch tensor (stays on the device)."""
+        if hasattr(new_map, "is_cuda") and new_map.is_cuda:
+            assert new_map.dim() == 2 and new_map.stride(1) == 1 and new_map.element_size() == 1
+            self.length, self.width = int(new_map.shape[0]), int(new_map.shape[1])
+            rc = self._L.tasi_set_map_device(self._h, C.c_void_p(new_map.data_ptr()), self.width, self.length,
+                                             int(new_map.stride(0)))
+            return self._check(rc)
+        a = np.ascontiguousarray(new_map, dtype=np.uint8)
+        if w is not None and h is not None:
+            a = a.reshape(h, w)
+        self.length, self.width = a.shape
+        return self._check(self._L.tasi_set_map(self._h, a.ctypes.data_as(C.c_void_p), self.width, self.length))
+
+    def patch_map(self, patch, x, y, w=None, h=None):
+        """Rows x..x+h-1, columns y..y+w-1 take `patch` (h rows of w) — Graph::update argument order."""
+        a = np.ascontiguousarray(patch, dtype=np.uint8)
+        if w is not None and h is not None:
+            a = a.reshape(h, w)
+        hh, ww = a.shape
+        n = C.c_uint64(0)
+        self._check(self._L.tasi_patch_map(self._h, a.ctypes.data_as(C.c_void_p), x, y, ww, hh, C.byref(n)))
+        return n.value
+
+    def set_start(self, x, y=None):
+        if y is None:
+            x, y = x
+        self._check(self._L.tasi_set_start(self._h, x, y))
+
+    def set_goal(self, x, y=None):
+        if y is None:
+            x, y = x
+        self._check(self._L.tasi_set_goal(self._h, x, y))
+
+    def step(self):
+        u, p = C.c_float(0), C.c_float(0)
+        nu, ne = C.c_uint64(0), C.c_uint64(0)
+        rc = self._check(self._L.tasi_step(self._h, C.byref(u), C.byref(p), C.byref(nu), C.byref(ne)))
+        if rc == LOOP_OK:
+            self.u_time, self.p_time = u.value, p.value
+            self.num_nodes_updated, self.num_nodes_expanded = nu.value, ne.value
+        return rc
+
+    def get_expanded_map(self):
+        return FieldView(self)
+
+    # -- field access -----------------------------------------------------------------------------------------
+    def field_dims(self):
+        ex, ey = C.c_int(0), C.c_int(0)
+        self._check(self._L.tasi_field_dims(self._h, C.byref(ex), C.byref(ey)))
+        return ex.value, ey.value
+
+    def read_field(self):
+        ex, ey = self.field_dims()
+        out = np.empty((ex, ey), np.float32)
+        self._check(self._L.tasi_read_field(self._h, out.ctypes.data_as(C.c_void_p)))
+        return out
+
+    def read_window(self, x0, y0, nx, ny, out=None):
+        if out is None:
+            out = np.empty((nx, ny), np.float32)
+        self._check(self._L.tasi_read_window(self._h, x0, y0, nx, ny, out.ctypes.data_as(C.c_void_p)))
+        return out
+
+    def read_map(self):
+        out = np.empty((self.length, self.width), np.uint8)
+        self._check(self._L.tasi_read_map(self._h, out.ctypes.data_as(C.c_void_p)))
+        return out
+
+    def synth_map(self, seed, width, length, row0=0, p_obs=10, start=None, goal=None):
+        """Generate the synthetic map of synth.py on the device; start/goal are GLOBAL cell coordinates."""
+        sx, sy = (int(round(start[0])), int(round(start[1]))) if start is not None else (-1, -1)
+        gx, gy = (int(round(goal[0])), int(round(goal[1]))) if goal is not None else (-1, -1)
+        self.length, self.width = length, width
+        self._check(self._L.tasi_synth_map(self._h, seed, width, length, row0, p_obs, sx, sy, gx, gy))
+
+    def stats(self):
+        s = _lib.Stats()
+        self._check(self._L.tasi_get_stats(self._h, C.byref(s)))
+        return s.as_dict()
+
+    def field_device(self):
+        ptr, pitch = C.c_void_p(), C.c_int64(0)
+        self._check(self._L.tasi_field_device(self._h, C.byref(ptr), C.byref(pitch)))
+        return ptr.value, pitch.value
+
+    # -- row bands ---------------------------------------------------------------------------------------------
+    def band_config(self, global_row0, open_top, open_bottom):
+        self._check(self._L.tasi_band_config(self._h, global_row0, int(open_top), int(open_bottom)))
+
+    def band_rows(self, side):
+        s, r, n = C.c_void_p(), C.c_void_p(), C.c_int64(0)
+        self._check(self._L.tasi_band_rows(self._h, side, C.byref(s), C.byref(r), C.byref(n)))
+        return s.value, r.value, n.value
+
+    def band_import(self, side):
+        n = C.c_uint64(0)
+        self._check(self._L.tasi_band_import(self._h, side, C.byref(n)))
+        return n.value
+
+    def band_begin(self):
+        return self._check(self._L.tasi_band_begin(self._h))
+
+    def band_solve(self):
+        n = C.c_uint64(0)
+        self._check(self._L.tasi_band_solve(self._h, C.byref(n)))
+        return n.value
+
+
+class FieldDPlanner(GpuPlanner):
+    """FD* — FieldDPlanner<OPT_LVL> (FieldDStar/FieldDPlanner.h); values on nodes."""
+    kind = FD
+    max_level = 1
+
+
+class DFMPlanner(GpuPlanner):
+    """MS-DFM — DFMPlanner<OPT_LVL> (DynamicFastMarching/DynamicFastMarching.h); values on cells."""
+    kind = DFM
+    max_level = 1
+
+
+class ShiftedGridPlanner(GpuPlanner):
+    """MFD* — ShiftedGridPlanner<OPT_LVL> (ShiftedGridFastMarching/ShiftedGridPlanner.h); values on nodes."""
+    kind = MFD
+    max_level = 2
+
+
+PLANNERS = {FD: FieldDPlanner, DFM: DFMPlanner, MFD: ShiftedGridPlanner}

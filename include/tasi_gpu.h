@@ -49,6 +49,8 @@ typedef struct tasi_stats {
     uint64_t inval_visits;     /* tile visits of the invalidate phase of a replan */
     uint64_t elem_invalidated; /* elements reset to INF by the invalidate phase */
     uint64_t seed_elems;       /* elements seeded by the last patch (== num_nodes_updated) */
+    uint64_t phases;           /* advances of the near/far threshold (tile-level Delta-stepping) */
+    uint64_t far_parked;       /* activations parked in the far pile */
     float kernel_ms_solve;     /* CUDA-event time of the solver kernel(s), re-propagation phase */
     float kernel_ms_inval;     /* CUDA-event time of the invalidate phase */
     float kernel_ms_init;      /* field fill / seeding kernels */

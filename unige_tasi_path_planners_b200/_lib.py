@@ -27,7 +27,8 @@ _ip = C.POINTER(C.c_int)
 class Stats(C.Structure):
     _fields_ = [("tiles", C.c_uint64), ("tile_visits", C.c_uint64), ("tile_rounds", C.c_uint64),
                 ("elem_lowered", C.c_uint64), ("queue_pushes", C.c_uint64), ("inval_visits", C.c_uint64),
-                ("elem_invalidated", C.c_uint64), ("seed_elems", C.c_uint64), ("kernel_ms_solve", C.c_float),
+                ("elem_invalidated", C.c_uint64), ("seed_elems", C.c_uint64), ("phases", C.c_uint64),
+                ("far_parked", C.c_uint64), ("kernel_ms_solve", C.c_float),
                 ("kernel_ms_inval", C.c_float), ("kernel_ms_init", C.c_float), ("solver_blocks", C.c_int32),
                 ("solver_launches", C.c_int32)]
 

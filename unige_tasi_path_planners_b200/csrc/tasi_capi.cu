@@ -44,6 +44,12 @@ struct tasi_planner {
     int64_t gpitch = 0, cpitch = 0, g_rows = 0;
     int *state = nullptr, *queue = nullptr;
     uint8_t *seed = nullptr;
+    int *key = nullptr, *far = nullptr;
+    int far_cap = 0;
+    unsigned long long *cost_sum = nullptr;  // device: {sum of free-cell costs, number of free cells}
+    bool cost_stats_valid = false;
+    float mean_cost = 1.0f;
+    float delta_factor = 0.5f;
     DevCtl *ctl = nullptr;
     float *stage = nullptr;  // 2 x EY receive rows (band mode)
     uint8_t *patch_buf = nullptr, *chg_buf = nullptr;
@@ -92,13 +98,16 @@ GridDesc make_desc(const tasi_planner *p) {
     d.pin_x = (int) px; d.pin_y = (int) py;
     d.state = p->state; d.queue = p->queue; d.qmask = p->qsize - 1;
     d.seed = p->seed; d.ctl = p->ctl;
+    d.key = p->key; d.far = p->far; d.far_cap = p->far_cap;
+    d.delta = p->delta_factor * (float) TS * p->mean_cost;
     d.inval_tol = (p->kind == TASI_DFM) ? 1e-6f : 0.0f;
     return d;
 }
 
 void free_grid(tasi_planner *p) {
     cudaFree(p->g_base); cudaFree(p->c_base); cudaFree(p->state); cudaFree(p->queue); cudaFree(p->seed);
-    cudaFree(p->stage);
+    cudaFree(p->stage); cudaFree(p->key); cudaFree(p->far);
+    p->key = nullptr; p->far = nullptr;
     p->g_base = nullptr; p->c_base = nullptr; p->state = nullptr; p->queue = nullptr; p->seed = nullptr;
     p->stage = nullptr;
 }
@@ -151,6 +160,9 @@ int alloc_grid(tasi_planner *p, int W, int rows) {
     CU_TRY(p, cudaMalloc(&p->state, sizeof(int) * nt));
     CU_TRY(p, cudaMalloc(&p->queue, sizeof(int) * q));
     CU_TRY(p, cudaMalloc(&p->seed, nt));
+    p->far_cap = 2 * nt + 64;
+    CU_TRY(p, cudaMalloc(&p->key, sizeof(int) * (size_t) ((nt + 3) / 4 * 4)));
+    CU_TRY(p, cudaMalloc(&p->far, sizeof(int) * 2 * (size_t) p->far_cap));
     CU_TRY(p, cudaMalloc(&p->stage, sizeof(float) * 2 * (size_t) EY));
     CU_TRY(p, cudaMemsetAsync(p->c_base, 255, (size_t) p->cpitch * p->g_rows, p->stream));
     CU_TRY(p, cudaMemsetAsync(p->state, 0, sizeof(int) * nt, p->stream));
@@ -172,13 +184,34 @@ int read_ctl(tasi_planner *p, DevCtl *h) {
     return TASI_OK;
 }
 
+// Mean free-cell cost of the current map (lazily, once per set_map): the band width of the schedule scales with it.
+int ensure_cost_stats(tasi_planner *p) {
+    if (p->cost_stats_valid) return TASI_OK;
+    if (!p->cost_sum) CU_TRY(p, cudaMalloc(&p->cost_sum, 2 * sizeof(unsigned long long)));
+    CU_TRY(p, cudaMemsetAsync(p->cost_sum, 0, 2 * sizeof(unsigned long long), p->stream));
+    // sample at most ~16M cells: whole rows from the top of the band
+    const int rows = (int) std::min<int64_t>(p->rows, std::max<int64_t>(1, (int64_t) (1 << 24) / p->W));
+    cost_stats_kernel<<<p->num_sms * 4, 256, 0, p->stream>>>(c_origin(p), p->cpitch, rows, p->W, p->thr, p->cost_sum);
+    CU_TRY(p, cudaGetLastError());
+    unsigned long long h[2];
+    CU_TRY(p, cudaMemcpyAsync(h, p->cost_sum, sizeof h, cudaMemcpyDeviceToHost, p->stream));
+    CU_TRY(p, cudaStreamSynchronize(p->stream));
+    p->mean_cost = h[1] ? (float) ((double) h[0] / (double) h[1]) : 1.0f;
+    if (p->mean_cost < 1.0f) p->mean_cost = 1.0f;
+    p->cost_stats_valid = true;
+    return TASI_OK;
+}
+
 // Queue the flagged tiles and run the persistent solver in `mode` until the queue drains.
 // Adds the launch's counters to p->stats; *ms = CUDA-event time of the three launches.
 int run_solver(tasi_planner *p, int mode, float *ms) {
+    int rcs = ensure_cost_stats(p);
+    if (rcs != TASI_OK) return rcs;
     GridDesc d = make_desc(p);
     DevCtl z;
     memset(&z, 0, sizeof z);
     z.timeout_ns = (unsigned long long) (p->timeout_s * 1e9);
+    z.thr_bits = (mode == 1 || p->delta_factor <= 0.0f) ? INF_BITS : 0;  // invalidation needs no order
     // reset queue tickets + per-launch counters, keep the patch bookkeeping
     CU_TRY(p, cudaMemcpyAsync(p->ctl, &z, offsetof(DevCtl, n_changed), cudaMemcpyHostToDevice, p->stream));
     CU_TRY(p, cudaEventRecord(p->ev0, p->stream));
@@ -194,6 +227,8 @@ int run_solver(tasi_planner *p, int mode, float *ms) {
     CU_TRY(p, cudaEventElapsedTime(ms, p->ev0, p->ev1));
     p->stats.solver_launches += 3;
     p->stats.queue_pushes += h.pushes;
+    p->stats.phases += (uint64_t) h.phases;
+    p->stats.far_parked += h.far_parked;
     if (mode == 0) {
         p->stats.tile_visits += h.visits;
         p->stats.tile_rounds += h.rounds;
@@ -221,6 +256,7 @@ int init_field(tasi_planner *p) {
     CU_TRY(p, cudaMemsetAsync(p->state, 0, sizeof(int) * nt, p->stream));
     const int64_t n4 = p->gpitch * p->g_rows / 4;
     fill_inf_kernel<<<p->num_sms * 8, 256, 0, p->stream>>>((float4 *) p->g_base, n4);
+    fill_inf_kernel<<<64, 256, 0, p->stream>>>((float4 *) p->key, (nt + 3) / 4);
     seed_goal_kernel<<<1, 1, 0, p->stream>>>(d);
     CU_TRY(p, cudaGetLastError());
     // patch bookkeeping restarts: the first plan reads the patched grid (ReplannerBase.h:52)
@@ -259,6 +295,7 @@ int tasi_create(int kind, int level, int device, tasi_planner **out) {
         double v = atof(e);
         if (v > 0) p->timeout_s = v;
     }
+    if (const char *e = getenv("TASI_DELTA_FACTOR")) p->delta_factor = (float) atof(e);  // <= 0: no ordering
     *out = p;
     return TASI_OK;
 }
@@ -268,7 +305,7 @@ int tasi_destroy(tasi_planner *p) {
     cudaSetDevice(p->device);
     if (p->stream) cudaStreamSynchronize(p->stream);
     free_grid(p);
-    cudaFree(p->ctl); cudaFree(p->patch_buf); cudaFree(p->chg_buf);
+    cudaFree(p->ctl); cudaFree(p->cost_sum); cudaFree(p->patch_buf); cudaFree(p->chg_buf);
     if (p->ev0) cudaEventDestroy(p->ev0);
     if (p->ev1) cudaEventDestroy(p->ev1);
     if (p->stream) cudaStreamDestroy(p->stream);
@@ -306,6 +343,7 @@ static int set_map_common(tasi_planner *p, const uint8_t *src, int width, int le
                                 kind, p->stream));
     CU_TRY(p, cudaStreamSynchronize(p->stream));  // the host pointer is not retained
     p->initialize_graph = false;
+    p->cost_stats_valid = false;
     return TASI_OK;
 }
 
@@ -329,6 +367,7 @@ int tasi_synth_map(tasi_planner *p, uint64_t seed, int width, int length, int64_
     CU_TRY(p, cudaGetLastError());
     CU_TRY(p, cudaStreamSynchronize(p->stream));
     p->initialize_graph = false;
+    p->cost_stats_valid = false;
     return TASI_OK;
 }
 

@@ -32,6 +32,8 @@ constexpr int CP = 35;         // shared-memory pitch of the cost tile (33 used 
 constexpr int NTHREADS = 128;  // 4 warps = 4 sweep directions
 constexpr int ST_DIRTY = 1;
 constexpr int ST_RUN = 2;
+constexpr int ST_FAR = 4;      // queued, but parked in the far pile (key >= current threshold)
+constexpr int INF_BITS = 0x7f800000;
 constexpr int GMARGIN = 32;    // columns of margin left of element/cell column 0 (keeps rows 128B aligned)
 
 struct DevCtl {
@@ -39,9 +41,13 @@ struct DevCtl {
     int pending;                    // tiles queued or running
     int done;                       // set when pending drops to 0 (or on error)
     int error;                      // 1 = watchdog fired
-    int pad0;
+    int thr_bits;                   // float bits of the near/far threshold: tiles keyed below it run now
     unsigned long long visits, rounds, lowered, pushes, invalidated;
     unsigned long long timeout_ns;
+    int far_sel;                    // which of the two far lists takes new entries
+    int far_count[2];
+    int phases;                     // threshold advances
+    unsigned long long far_parked;  // activations that went to the far pile
     // patch bookkeeping
     unsigned long long n_changed, n_raised, n_lowered_cells, n_seed_elems;
     unsigned long long halo_lowered;
@@ -61,6 +67,10 @@ struct GridDesc {
     int *queue;            // ring of tile id + 1, 0 = empty
     unsigned qmask;        // ring size - 1
     uint8_t *seed;         // TX*TY: tiles to enqueue before the next solver launch
+    int *key;              // TX*TY: float bits of the lowest value that entered the tile since its last visit
+    int *far;              // 2 * far_cap tile ids: the far pile, double-buffered
+    int far_cap;
+    float delta;           // width of the value band processed per phase
     DevCtl *ctl;
     float inval_tol;       // relative slack of the invalidate test (0 for FD*/MFD*)
 };
@@ -109,12 +119,100 @@ __device__ inline int q_pop(const GridDesc &d) {
     }
 }
 
-__device__ __forceinline__ void activate(const GridDesc &d, int tile) {
-    int old = atomicOr(&d.state[tile], ST_DIRTY);
-    if (old == 0) {
+// ---- near / far scheduling -------------------------------------------------------------------------------------
+// Every activation carries a key: the lowest changed value the tile is about to read. Tiles keyed below the
+// current threshold go to the work queue ("near"); the others are parked in the far pile until the queue has
+// drained and the threshold advances by `delta` (a tile-level Delta-stepping order: without it a
+// label-correcting solve revisits each tile dozens of times, with it a few).
+__device__ __forceinline__ int cur_thr_bits(const GridDesc &d) { return *(volatile int *) &d.ctl->thr_bits; }
+
+// park a tile whose state already carries ST_FAR; falls back to the queue if the pile is full
+__device__ inline void far_append(const GridDesc &d, int tile) {
+    const int sel = *(volatile int *) &d.ctl->far_sel;
+    const int slot = atomicAdd(&d.ctl->far_count[sel], 1);
+    if (slot < d.far_cap) {
+        d.far[sel * d.far_cap + slot] = tile;
+        __threadfence();
+        atomicAdd(&d.ctl->far_parked, 1ULL);
+    } else {
+        atomicAnd(&d.state[tile], ~ST_FAR);
         q_push(d, tile);
         atomicAdd(&d.ctl->pushes, 1ULL);
     }
+}
+
+__device__ inline void activate(const GridDesc &d, int tile, int kbits) {
+    atomicMin(&d.key[tile], kbits);
+    const bool near = kbits < cur_thr_bits(d);
+    int old = atomicCAS(&d.state[tile], 0, near ? ST_DIRTY : (ST_DIRTY | ST_FAR));
+    if (old != 0) {
+        old = atomicOr(&d.state[tile], ST_DIRTY);
+        if (old == 0 && !near) atomicOr(&d.state[tile], ST_FAR);  // it went idle in between: ours to queue
+    }
+    if (old == 0) {
+        if (near) {
+            q_push(d, tile);
+            atomicAdd(&d.ctl->pushes, 1ULL);
+        } else {
+            far_append(d, tile);
+        }
+    } else if ((old & ST_FAR) && near) {
+        // parked with a higher key: promote (whoever clears ST_FAR owns the push; the pile entry goes stale)
+        if (atomicAnd(&d.state[tile], ~ST_FAR) & ST_FAR) {
+            q_push(d, tile);
+            atomicAdd(&d.ctl->pushes, 1ULL);
+        }
+    }
+}
+
+// The queue has drained and no tile is running: raise the threshold to (lowest parked key + delta) and move
+// the parked tiles below it into the queue. Runs on ONE CTA while all others wait in q_pop, so the pile is
+// not appended to until the first push below. Returns with s_flag = 1 if nothing is left anywhere.
+__device__ inline void advance_threshold(const GridDesc &d, int *s_red, int tid) {
+    DevCtl *c = d.ctl;
+    const int cur = *(volatile int *) &c->far_sel;
+    const int n = min(*(volatile int *) &c->far_count[cur], d.far_cap);
+    const int *src = d.far + cur * d.far_cap;
+    int m = INF_BITS;
+    for (int i = tid; i < n; i += NTHREADS) {
+        const int t = __ldcg(src + i);
+        if (*(volatile int *) &d.state[t] & ST_FAR) m = min(m, *(volatile int *) &d.key[t]);
+    }
+    m = __reduce_min_sync(0xffffffffu, m);
+    if ((tid & 31) == 0) s_red[tid >> 5] = m;
+    __syncthreads();
+    m = min(min(s_red[0], s_red[1]), min(s_red[2], s_red[3]));
+    int nthr = INF_BITS;
+    if (m != INF_BITS) {
+        const float t = __int_as_float(m) + d.delta;
+        nthr = __float_as_int(t);
+        if (nthr <= m) nthr = m + 1;  // delta lost to rounding: still let the lowest tile through
+    }
+    if (tid == 0) {
+        c->thr_bits = nthr;
+        c->far_count[cur ^ 1] = 0;
+        c->far_sel = cur ^ 1;  // new parkings (from the tiles pushed below) go to the other list
+        atomicAdd(&c->phases, 1);
+        __threadfence();
+    }
+    __syncthreads();
+    int *dst = d.far + (cur ^ 1) * d.far_cap;
+    for (int i = tid; i < n; i += NTHREADS) {
+        const int t = __ldcg(src + i);
+        if (!(*(volatile int *) &d.state[t] & ST_FAR)) continue;  // stale entry (tile was promoted)
+        if (*(volatile int *) &d.key[t] < nthr || nthr == INF_BITS) {
+            if (atomicAnd(&d.state[t], ~ST_FAR) & ST_FAR) {
+                q_push(d, t);
+                atomicAdd(&c->pushes, 1ULL);
+            }
+        } else {
+            const int slot = atomicAdd(&c->far_count[cur ^ 1], 1);
+            if (slot < d.far_cap) dst[slot] = t;
+            else if (atomicAnd(&d.state[t], ~ST_FAR) & ST_FAR) q_push(d, t);
+        }
+    }
+    __syncthreads();
+    if (tid == 0) c->far_count[cur] = 0;
 }
 
 // ---- one directional sweep of a staged tile by one warp ------------------------------------------------------
@@ -175,7 +273,9 @@ __global__ void __launch_bounds__(NTHREADS) solver_kernel(GridDesc d) {
     __shared__ float sg[(TS + 2) * GP];   // values, rows/cols -1..32
     __shared__ float sg0[TS * TS];        // interior as loaded (change detection at write-back)
     __shared__ float sc[(TS + 1) * CP];   // cell costs as float, INF = obstacle
-    __shared__ int s_tile, s_mask, s_again;
+    __shared__ int s_tile, s_again, s_adv;
+    __shared__ int s_kmin[8];             // per neighbour direction: lowest changed value it will read (bits)
+    __shared__ int s_red[NTHREADS / 32];
 
     const float INF = __int_as_float(0x7f800000);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -185,12 +285,13 @@ __global__ void __launch_bounds__(NTHREADS) solver_kernel(GridDesc d) {
         if (tid == 0) {
             int t = q_pop(d);
             if (t >= 0) {
+                atomicExch(&d.key[t], INF_BITS);
                 atomicExch(&d.state[t], ST_RUN);  // clears DIRTY: everything written before it was set is
                 __threadfence();                  // visible to the loads below
             }
             s_tile = t;
-            s_mask = 0;
         }
+        if (tid < 8) s_kmin[tid] = INF_BITS;
         __syncthreads();
         const int tile = s_tile;
         if (tile < 0) break;
@@ -233,57 +334,88 @@ __global__ void __launch_bounds__(NTHREADS) solver_kernel(GridDesc d) {
                 if (!__syncthreads_or(ch)) break;
             }
 
-            // write back what changed, note which borders moved
-            int m = 0;
+            // write back what changed; per neighbour direction keep the lowest changed value it reads
+            // (invalidate mode: the old value, which is what the neighbour's elements were supported by)
             for (int i = tid; i < TS * TS; i += NTHREADS) {
                 const int r = i >> 5, c = i & 31;
                 const float v = sg[(r + 1) * GP + (c + 1)];
-                if (v != sg0[i]) {
+                const float v0 = sg0[i];
+                if (v != v0) {
                     d.g[(int64_t) (x0 + r) * d.gpitch + (y0 + c)] = v;
-                    if (r == 0) m |= NB_N | (c == 0 ? NB_NW : 0) | (c == TS - 1 ? NB_NE : 0);
-                    if (r == TS - 1) m |= NB_S | (c == 0 ? NB_SW : 0) | (c == TS - 1 ? NB_SE : 0);
-                    if (c == 0) m |= NB_W;
-                    if (c == TS - 1) m |= NB_E;
+                    const int kb = __float_as_int(MODE == 0 ? v : v0);
+                    if (r == 0) {
+                        atomicMin(&s_kmin[0], kb);
+                        if (c == 0) atomicMin(&s_kmin[4], kb);
+                        if (c == TS - 1) atomicMin(&s_kmin[5], kb);
+                    }
+                    if (r == TS - 1) {
+                        atomicMin(&s_kmin[1], kb);
+                        if (c == 0) atomicMin(&s_kmin[6], kb);
+                        if (c == TS - 1) atomicMin(&s_kmin[7], kb);
+                    }
+                    if (c == 0) atomicMin(&s_kmin[2], kb);
+                    if (c == TS - 1) atomicMin(&s_kmin[3], kb);
                 }
             }
-            m = __reduce_or_sync(0xffffffffu, m);
-            if (lane == 0 && m) atomicOr(&s_mask, m);
             __threadfence();
             __syncthreads();
 
             if (tid == 0) {
-                const int mk = s_mask;
-                s_mask = 0;
                 if (MODE == 1) d.seed[tile] = 1;  // phase 2 revisits every tile phase 1 looked at
                 const bool hn = tx > 0, hs = tx + 1 < d.TX, hw = ty > 0, he = ty + 1 < d.TY;
-                if ((mk & NB_N) && hn) activate(d, tile - d.TY);
-                if ((mk & NB_S) && hs) activate(d, tile + d.TY);
-                if ((mk & NB_W) && hw) activate(d, tile - 1);
-                if ((mk & NB_E) && he) activate(d, tile + 1);
-                if ((mk & NB_NW) && hn && hw) activate(d, tile - d.TY - 1);
-                if ((mk & NB_NE) && hn && he) activate(d, tile - d.TY + 1);
-                if ((mk & NB_SW) && hs && hw) activate(d, tile + d.TY - 1);
-                if ((mk & NB_SE) && hs && he) activate(d, tile + d.TY + 1);
+                int k;
+                if ((k = s_kmin[0]) != INF_BITS && hn) activate(d, tile - d.TY, k);
+                if ((k = s_kmin[1]) != INF_BITS && hs) activate(d, tile + d.TY, k);
+                if ((k = s_kmin[2]) != INF_BITS && hw) activate(d, tile - 1, k);
+                if ((k = s_kmin[3]) != INF_BITS && he) activate(d, tile + 1, k);
+                if ((k = s_kmin[4]) != INF_BITS && hn && hw) activate(d, tile - d.TY - 1, k);
+                if ((k = s_kmin[5]) != INF_BITS && hn && he) activate(d, tile - d.TY + 1, k);
+                if ((k = s_kmin[6]) != INF_BITS && hs && hw) activate(d, tile + d.TY - 1, k);
+                if ((k = s_kmin[7]) != INF_BITS && hs && he) activate(d, tile + d.TY + 1, k);
+                for (int j = 0; j < 8; ++j) s_kmin[j] = INF_BITS;
                 // leave the tile, unless a neighbour changed our halo meanwhile
+                int again_f = 0;
                 int old = atomicCAS(&d.state[tile], ST_RUN, 0);
-                if (old != ST_RUN) {
-                    atomicExch(&d.state[tile], ST_RUN);
-                    __threadfence();
-                    s_again = 1;
-                } else {
-                    s_again = 0;
+                if (old != ST_RUN) {  // RUN|DIRTY
+                    const int kk = atomicMin(&d.key[tile], INF_BITS);  // atomic read
+                    if (kk < cur_thr_bits(d) || kk == INF_BITS) {
+                        // due now (or key lost to the reset race): keep the tile and go round again
+                        atomicExch(&d.key[tile], INF_BITS);
+                        atomicExch(&d.state[tile], ST_RUN);
+                        __threadfence();
+                        again_f = 1;
+                    } else {
+                        atomicExch(&d.state[tile], ST_DIRTY | ST_FAR);
+                        far_append(d, tile);
+                    }
                 }
-                if (*(volatile int *) &d.ctl->error) s_again = 0;
+                if (*(volatile int *) &d.ctl->error) again_f = 0;
+                s_again = again_f;
             }
             __syncthreads();
             again = s_again != 0;
         } while (again);
 
-        if (tid == 0) {
-            if (atomicSub(&d.ctl->pending, 1) == 1) {
-                __threadfence();
-                atomicExch(&d.ctl->done, 1);
+        // the tile is no longer pending; whoever takes the count to 0 advances the threshold
+        if (tid == 0) s_adv = (atomicSub(&d.ctl->pending, 1) == 1) ? 1 : 0;
+        __syncthreads();
+        while (s_adv) {
+            __syncthreads();
+            if (tid == 0) atomicAdd(&d.ctl->pending, 1);  // hold the count while tiles are being pushed
+            advance_threshold(d, s_red, tid);
+            __syncthreads();
+            if (tid == 0) {
+                int more = 0;
+                if (atomicSub(&d.ctl->pending, 1) == 1) {
+                    // nothing was pushed (or all of it already finished)
+                    const int sel = *(volatile int *) &d.ctl->far_sel;
+                    if (*(volatile int *) &d.ctl->far_count[sel] > 0) more = 1;
+                    else { __threadfence(); atomicExch(&d.ctl->done, 1); }
+                }
+                if (*(volatile int *) &d.ctl->error) more = 0;
+                s_adv = more;
             }
+            __syncthreads();
         }
     }
 
@@ -409,6 +541,26 @@ __global__ void band_import_kernel(GridDesc d, const float *stage, int hrow, int
         }
     }
     if (cnt) atomicAdd(&d.ctl->halo_lowered, cnt);
+}
+
+// Sum and count of the free-cell costs (sizes the value band of the near/far schedule).
+__global__ void cost_stats_kernel(const uint8_t *cost, int64_t cpitch, int rows, int W, int thr,
+                                  unsigned long long *out) {
+    const int64_t n = (int64_t) rows * W;
+    unsigned long long sum = 0, cnt = 0;
+    for (int64_t i = blockIdx.x * (int64_t) blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x) {
+        const int r = (int) (i / W), c = (int) (i - (int64_t) r * W);
+        const uint8_t b = cost[(int64_t) r * cpitch + c];
+        if (b < thr) { sum += b; ++cnt; }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        sum += __shfl_down_sync(0xffffffffu, sum, o);
+        cnt += __shfl_down_sync(0xffffffffu, cnt, o);
+    }
+    if ((threadIdx.x & 31) == 0 && cnt) {
+        atomicAdd(&out[0], sum);
+        atomicAdd(&out[1], cnt);
+    }
 }
 
 // Deterministic synthetic traversability grid (same function as synth.py):

@@ -43,7 +43,8 @@ typedef struct tasi_planner tasi_planner;
 typedef struct tasi_stats {
     uint64_t tiles;            /* 32x32 tiles of the element grid */
     uint64_t tile_visits;      /* tiles staged into shared memory (solve phase) */
-    uint64_t tile_rounds;      /* in-tile relaxation rounds (4 directional sweeps each) */
+    uint64_t tile_rounds;      /* in-tile relaxation iterations (one pass over the tile's dirty elements) */
+    uint64_t elem_evals;       /* element evaluations (local updates computed) in the solve phase */
     uint64_t elem_lowered;     /* accepted decreases of an element value */
     uint64_t queue_pushes;     /* tile activations that entered the work queue */
     uint64_t inval_visits;     /* tile visits of the invalidate phase of a replan */

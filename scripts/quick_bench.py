@@ -26,6 +26,7 @@ for N in sizes:
                 best = dict(s, wall_ms=dt * 1e3, rc=rc)
         best.update(kind=kind, N=N, mcells_s=N * N / best["kernel_ms_solve"] / 1e3,
                     visits_per_tile=best["tile_visits"] / best["tiles"],
-                    rounds_per_visit=best["tile_rounds"] / max(best["tile_visits"], 1))
+                    rounds_per_visit=best["tile_rounds"] / max(best["tile_visits"], 1),
+                    evals_per_elem=best["elem_evals"] / (N * N), lowered_per_elem=best["elem_lowered"] / (N * N))
         print(json.dumps(best), flush=True)
         p.close()

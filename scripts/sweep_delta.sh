@@ -6,6 +6,6 @@ for f in 0 0.125 0.25 0.5 1 2; do
 import sys, json
 for l in sys.stdin:
     d = json.loads(l)
-    print(d['kind'], d['N'], 'ms=%.2f' % d['kernel_ms_solve'], 'Mc/s=%.0f' % d['mcells_s'], 'vis/tile=%.2f' % d['visits_per_tile'], 'rnd/vis=%.2f' % d['rounds_per_visit'], 'phases', d['phases'], 'rc', d['rc'])
+    print(d['kind'], d['N'], 'ms=%.2f' % d['kernel_ms_solve'], 'Mc/s=%.0f' % d['mcells_s'], 'vis/tile=%.2f' % d['visits_per_tile'], 'rnd/vis=%.2f' % d['rounds_per_visit'], 'ev/el=%.1f' % d['evals_per_elem'], 'low/el=%.1f' % d['lowered_per_elem'], 'phases', d['phases'], 'blk', d['solver_blocks'], 'rc', d['rc'])
 "
 done

@@ -25,7 +25,7 @@ _ip = C.POINTER(C.c_int)
 
 
 class Stats(C.Structure):
-    _fields_ = [("tiles", C.c_uint64), ("tile_visits", C.c_uint64), ("tile_rounds", C.c_uint64),
+    _fields_ = [("tiles", C.c_uint64), ("tile_visits", C.c_uint64), ("tile_rounds", C.c_uint64), ("elem_evals", C.c_uint64),
                 ("elem_lowered", C.c_uint64), ("queue_pushes", C.c_uint64), ("inval_visits", C.c_uint64),
                 ("elem_invalidated", C.c_uint64), ("seed_elems", C.c_uint64), ("phases", C.c_uint64),
                 ("far_parked", C.c_uint64), ("kernel_ms_solve", C.c_float),

@@ -48,6 +48,7 @@ struct DevCtl {
     int far_count[2];
     int phases;                     // threshold advances
     unsigned long long far_parked;  // activations that went to the far pile
+    unsigned long long evals;       // element evaluations
     // patch bookkeeping
     unsigned long long n_changed, n_raised, n_lowered_cells, n_seed_elems;
     unsigned long long halo_lowered;
@@ -67,6 +68,7 @@ struct GridDesc {
     int *queue;            // ring of tile id + 1, 0 = empty
     unsigned qmask;        // ring size - 1
     uint8_t *seed;         // TX*TY: tiles to enqueue before the next solver launch
+    int *inmask;           // TX*TY: IN_* bits, which halo sides changed since the tile was last staged
     int *key;              // TX*TY: float bits of the lowest value that entered the tile since its last visit
     int *far;              // 2 * far_cap tile ids: the far pile, double-buffered
     int far_cap;
@@ -141,8 +143,10 @@ __device__ inline void far_append(const GridDesc &d, int tile) {
     }
 }
 
-__device__ inline void activate(const GridDesc &d, int tile, int kbits) {
+__device__ inline void activate(const GridDesc &d, int tile, int kbits, int dirbit) {
+    atomicOr(&d.inmask[tile], dirbit);
     atomicMin(&d.key[tile], kbits);
+    __threadfence();  // mask and key must be in place before the state says "queued"
     const bool near = kbits < cur_thr_bits(d);
     int old = atomicCAS(&d.state[tile], 0, near ? ST_DIRTY : (ST_DIRTY | ST_FAR));
     if (old != 0) {
@@ -215,79 +219,142 @@ __device__ inline void advance_threshold(const GridDesc &d, int *s_red, int tid)
     if (tid == 0) c->far_count[cur] = 0;
 }
 
-// ---- one directional sweep of a staged tile by one warp ------------------------------------------------------
-// dir 0: rows top->bottom (lane = column), 1: rows bottom->top, 2: columns left->right (lane = row),
-// 3: columns right->left. rlim/clim = number of owned rows/columns inside this tile (elements beyond the
-// grid are never written). MODE 0 relaxes (accept decreases), MODE 1 invalidates unsupported values.
+// ---- in-tile relaxation: cell-level active list -------------------------------------------------------------------
+// A staged tile keeps one dirty bit per element ("a neighbour changed since this element was last evaluated").
+// Warp w owns rows w, w+4, ..., w+28: every iteration it swaps its rows' dirty words out, compacts the set
+// bits into a list with a ballot-free popc/shuffle scan, evaluates 32 listed elements per instruction, and
+// an element that changed sets the dirty bits of its 8 neighbours (possibly in rows of other warps). The
+// tile is converged when an iteration finds no dirty bit in any warp (__syncthreads_or). Work is proportional
+// to the number of element updates, not to the tile area, so a revisit that only moves a thin strip is cheap.
+//
+// Direction bits: which halo side of a tile changed (set by the neighbour that wrote it); they select the
+// elements that are dirty when the tile is staged.
+constexpr int IN_N = 1, IN_S = 2, IN_W = 4, IN_E = 8, IN_NW = 16, IN_NE = 32, IN_SW = 64, IN_SE = 128, IN_ALL = 256;
+
+// value an element takes from its staged neighbours; sgp points at the element inside the staged tile
+template <int KIND>
+__device__ __forceinline__ float eval_elem(const volatile float *p, const float *sc, int r, int c) {
+    Nbr8 nb;
+    nb.n = p[-GP]; nb.s = p[GP]; nb.w = p[-1]; nb.e = p[1];
+    nb.nw = p[-GP - 1]; nb.ne = p[-GP + 1]; nb.sw = p[GP - 1]; nb.se = p[GP + 1];
+    if (KIND == TASI_KIND_DFM) {
+        return dfm_cell(nb, sc[r * CP + c]);
+    } else {
+        const float *q = sc + r * CP + c;  // sc[i][j] = cost of cell (x0-1+i, y0-1+j)
+        const float tl = q[0], tr = q[1], bl = q[CP], br = q[CP + 1];
+        return (KIND == TASI_KIND_FD) ? fd_node(nb, tl, tr, bl, br) : mfd_node(nb, tl, tr, bl, br);
+    }
+}
+
+// mark the 8 neighbours of (r,c) dirty (those inside the owned part of the tile)
+__device__ __forceinline__ void mark_neighbours(unsigned *dirty, int r, int c, int rlim, unsigned colmask) {
+    const unsigned three = (unsigned) ((7ull << c) >> 1);  // bits c-1, c, c+1 clipped to the 32 columns
+    const unsigned m3 = three & colmask;
+    const unsigned m2 = m3 & ~(1u << c);
+    if (r > 0 && m3) atomicOr(&dirty[r - 1], m3);
+    if (m2) atomicOr(&dirty[r], m2);
+    if (r + 1 < rlim && m3) atomicOr(&dirty[r + 1], m3);
+}
+
+// dirty bits of a freshly staged tile from the direction mask
+__device__ __forceinline__ unsigned initial_dirty(int inmask, int r, int rlim, unsigned colmask) {
+    if (r >= rlim) return 0u;
+    unsigned w = 0;
+    if (inmask & IN_ALL) w = 0xffffffffu;
+    if ((inmask & IN_N) && r == 0) w = 0xffffffffu;
+    if ((inmask & IN_S) && r == TS - 1) w = 0xffffffffu;
+    if (inmask & IN_W) w |= 1u;
+    if (inmask & IN_E) w |= 0x80000000u;
+    if ((inmask & IN_NW) && r == 0) w |= 1u;
+    if ((inmask & IN_NE) && r == 0) w |= 0x80000000u;
+    if ((inmask & IN_SW) && r == TS - 1) w |= 1u;
+    if ((inmask & IN_SE) && r == TS - 1) w |= 0x80000000u;
+    return w & colmask;
+}
+
+// Relax (MODE 0) or invalidate (MODE 1) the staged tile to local convergence. Returns this thread's count of
+// changed elements; *evals gets the number of element evaluations. chg[] accumulates which elements changed.
 template <int KIND, int MODE>
-__device__ __forceinline__ int sweep_tile(float *sg, const float *sc, int dir, int lane, int rlim, int clim,
-                                          int pin_r, int pin_c, float tol) {
+__device__ __forceinline__ int relax_tile(float *sg, const float *sc, unsigned *dirty, unsigned *chg,
+                                          unsigned short *wlist, int warp, int lane, int rlim, int clim, int pin_r,
+                                          int pin_c, float tol, unsigned &iters, unsigned &evals) {
     const float INF = __int_as_float(0x7f800000);
-    const bool rowmode = dir < 2;
-    const bool rev = dir & 1;
-    const int lim_line = rowmode ? rlim : clim;
-    const bool lane_ok = lane < (rowmode ? clim : rlim);
-    int cnt = 0;
-    for (int s = 0; s < TS; ++s) {
-        const int line = rev ? (TS - 1 - s) : s;
-        if (line < lim_line && lane_ok) {
-            const int r = rowmode ? line : lane;
-            const int c = rowmode ? lane : line;
-            volatile float *p = sg + (r + 1) * GP + (c + 1);
-            const float cur = *p;
-            Nbr8 nb;
-            nb.n = p[-GP]; nb.s = p[GP]; nb.w = p[-1]; nb.e = p[1];
-            nb.nw = p[-GP - 1]; nb.ne = p[-GP + 1]; nb.sw = p[GP - 1]; nb.se = p[GP + 1];
-            float v;
-            if (KIND == TASI_KIND_DFM) {
-                v = dfm_cell(nb, sc[r * CP + c]);
-            } else {
-                const float *q = sc + r * CP + c;  // sc[i][j] = cost of cell (x0-1+i, y0-1+j)
-                const float tl = q[0], tr = q[1], bl = q[CP], br = q[CP + 1];
-                v = (KIND == TASI_KIND_FD) ? fd_node(nb, tl, tr, bl, br) : mfd_node(nb, tl, tr, bl, br);
-            }
-            if (MODE == 0) {
-                if (v < cur) {
-                    // non-negative floats order like their bit patterns; concurrent sweeps never raise a value
-                    atomicMin((int *) (sg + (r + 1) * GP + (c + 1)), __float_as_int(v));
-                    ++cnt;
-                }
-            } else {
-                if (cur < INF && !(r == pin_r && c == pin_c) && v > cur + cur * tol) {
-                    *p = INF;
-                    ++cnt;
-                }
-            }
+    const unsigned colmask = clim >= 32 ? 0xffffffffu : ((1u << clim) - 1u);
+    const int row = warp + 4 * (lane >> 2);  // the row whose dirty word this lane helps to unpack
+    const int q = lane & 3;                  // which byte of the word
+    int cnt_changed = 0;
+    for (;;) {
+        unsigned word = 0;
+        if (q == 0) word = atomicExch(&dirty[row], 0u);
+        word = __shfl_sync(0xffffffffu, word, lane & ~3);
+        unsigned slice = (word >> (8 * q)) & 0xffu;
+        const int cnt = __popc(slice);
+        int incl = cnt;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += t;
+        }
+        const int total = __shfl_sync(0xffffffffu, incl, 31);
+        int pos = incl - cnt;
+        while (slice) {
+            const int b = __ffs(slice) - 1;
+            slice &= slice - 1;
+            wlist[pos++] = (unsigned short) ((row << 5) | (8 * q + b));
         }
         __syncwarp();
+        for (int i = lane; i < total; i += 32) {
+            const int rc = wlist[i];
+            const int r = rc >> 5, c = rc & 31;
+            volatile float *p = sg + (r + 1) * GP + (c + 1);
+            const float cur = *p;
+            const float v = eval_elem<KIND>(p, sc, r, c);
+            bool changed;
+            if (MODE == 0) {
+                changed = v < cur;
+                if (changed) *p = v;
+            } else {
+                changed = cur < INF && !(r == pin_r && c == pin_c) && v > cur + cur * tol;
+                if (changed) *p = INF;
+            }
+            if (changed) {
+                ++cnt_changed;
+                __threadfence_block();  // the value must be visible before the neighbours' dirty bits
+                mark_neighbours(dirty, r, c, rlim, colmask);
+                atomicOr(&chg[r], 1u << c);
+            }
+        }
+        evals += total;
+        ++iters;
+        if (!__syncthreads_or(total > 0)) break;
     }
-    return cnt;
+    return cnt_changed;
 }
 
 // ---- the persistent solver kernel ------------------------------------------------------------------------------
-// Border-change bits: which neighbour tiles read the cells that changed.
-constexpr int NB_N = 1, NB_S = 2, NB_W = 4, NB_E = 8, NB_NW = 16, NB_NE = 32, NB_SW = 64, NB_SE = 128;
-
 template <int KIND, int MODE>
 __global__ void __launch_bounds__(NTHREADS) solver_kernel(GridDesc d) {
     __shared__ float sg[(TS + 2) * GP];   // values, rows/cols -1..32
-    __shared__ float sg0[TS * TS];        // interior as loaded (change detection at write-back)
     __shared__ float sc[(TS + 1) * CP];   // cell costs as float, INF = obstacle
-    __shared__ int s_tile, s_again, s_adv;
+    __shared__ unsigned s_dirty[TS], s_chg[TS];
+    __shared__ unsigned short s_list[NTHREADS / 32][TS * TS / (NTHREADS / 32)];
+    __shared__ int s_tile, s_inmask, s_again, s_adv;
     __shared__ int s_kmin[8];             // per neighbour direction: lowest changed value it will read (bits)
     __shared__ int s_red[NTHREADS / 32];
 
     const float INF = __int_as_float(0x7f800000);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    unsigned long long n_visits = 0, n_rounds = 0, n_changed = 0;
+    unsigned long long n_visits = 0, n_iters = 0, n_changed = 0, n_evals = 0;
 
     for (;;) {
         if (tid == 0) {
             int t = q_pop(d);
             if (t >= 0) {
+                atomicExch(&d.state[t], ST_RUN);  // clears DIRTY; activations ordered before it are consumed below
+                __threadfence();
+                s_inmask = atomicExch(&d.inmask[t], 0);
                 atomicExch(&d.key[t], INF_BITS);
-                atomicExch(&d.state[t], ST_RUN);  // clears DIRTY: everything written before it was set is
-                __threadfence();                  // visible to the loads below
+                __threadfence();                  // ... and their values are visible to the loads below
             }
             s_tile = t;
         }
@@ -298,6 +365,7 @@ __global__ void __launch_bounds__(NTHREADS) solver_kernel(GridDesc d) {
         const int tx = tile / d.TY, ty = tile - tx * d.TY;
         const int x0 = tx * TS, y0 = ty * TS;
         const int rlim = min(TS, d.EX - x0), clim = min(TS, d.EY - y0);
+        const unsigned colmask = clim >= 32 ? 0xffffffffu : ((1u << clim) - 1u);
         const int pin_r = d.pin_x - x0, pin_c = d.pin_y - y0;
 
         // cell costs around the tile (immutable while the solver runs)
@@ -320,29 +388,31 @@ __global__ void __launch_bounds__(NTHREADS) solver_kernel(GridDesc d) {
             // stage values + halo ring; L1 is bypassed (other CTAs write these lines)
             for (int i = tid; i < (TS + 2) * (TS + 2); i += NTHREADS) {
                 const int r = i / (TS + 2), c = i - r * (TS + 2);
-                const float v = __ldcg(d.g + (int64_t) (x0 - 1 + r) * d.gpitch + (y0 - 1 + c));
-                sg[r * GP + c] = v;
-                if (r >= 1 && r <= TS && c >= 1 && c <= TS) sg0[(r - 1) * TS + (c - 1)] = v;
+                sg[r * GP + c] = __ldcg(d.g + (int64_t) (x0 - 1 + r) * d.gpitch + (y0 - 1 + c));
+            }
+            if (tid < TS) {
+                s_dirty[tid] = initial_dirty(s_inmask, tid, rlim, colmask);
+                s_chg[tid] = 0u;
             }
             __syncthreads();
             ++n_visits;
 
-            for (;;) {
-                const int ch = sweep_tile<KIND, MODE>(sg, sc, warp, lane, rlim, clim, pin_r, pin_c, d.inval_tol);
-                n_changed += ch;
-                ++n_rounds;
-                if (!__syncthreads_or(ch)) break;
-            }
+            unsigned it = 0, ev = 0;
+            n_changed += relax_tile<KIND, MODE>(sg, sc, s_dirty, s_chg, s_list[warp], warp, lane, rlim, clim, pin_r,
+                                                pin_c, d.inval_tol, it, ev);
+            n_iters += it;
+            n_evals += ev;
 
             // write back what changed; per neighbour direction keep the lowest changed value it reads
-            // (invalidate mode: the old value, which is what the neighbour's elements were supported by)
-            for (int i = tid; i < TS * TS; i += NTHREADS) {
-                const int r = i >> 5, c = i & 31;
-                const float v = sg[(r + 1) * GP + (c + 1)];
-                const float v0 = sg0[i];
-                if (v != v0) {
+            {
+                const int r = tid >> 2, qq = tid & 3;
+                unsigned slice = (s_chg[r] >> (8 * qq)) & 0xffu;
+                while (slice) {
+                    const int c = 8 * qq + __ffs(slice) - 1;
+                    slice &= slice - 1;
+                    const float v = sg[(r + 1) * GP + (c + 1)];
                     d.g[(int64_t) (x0 + r) * d.gpitch + (y0 + c)] = v;
-                    const int kb = __float_as_int(MODE == 0 ? v : v0);
+                    const int kb = (MODE == 0) ? __float_as_int(v) : 0;
                     if (r == 0) {
                         atomicMin(&s_kmin[0], kb);
                         if (c == 0) atomicMin(&s_kmin[4], kb);
@@ -364,14 +434,15 @@ __global__ void __launch_bounds__(NTHREADS) solver_kernel(GridDesc d) {
                 if (MODE == 1) d.seed[tile] = 1;  // phase 2 revisits every tile phase 1 looked at
                 const bool hn = tx > 0, hs = tx + 1 < d.TX, hw = ty > 0, he = ty + 1 < d.TY;
                 int k;
-                if ((k = s_kmin[0]) != INF_BITS && hn) activate(d, tile - d.TY, k);
-                if ((k = s_kmin[1]) != INF_BITS && hs) activate(d, tile + d.TY, k);
-                if ((k = s_kmin[2]) != INF_BITS && hw) activate(d, tile - 1, k);
-                if ((k = s_kmin[3]) != INF_BITS && he) activate(d, tile + 1, k);
-                if ((k = s_kmin[4]) != INF_BITS && hn && hw) activate(d, tile - d.TY - 1, k);
-                if ((k = s_kmin[5]) != INF_BITS && hn && he) activate(d, tile - d.TY + 1, k);
-                if ((k = s_kmin[6]) != INF_BITS && hs && hw) activate(d, tile + d.TY - 1, k);
-                if ((k = s_kmin[7]) != INF_BITS && hs && he) activate(d, tile + d.TY + 1, k);
+                // our north border is the south halo of the tile above, and so on
+                if ((k = s_kmin[0]) != INF_BITS && hn) activate(d, tile - d.TY, k, IN_S);
+                if ((k = s_kmin[1]) != INF_BITS && hs) activate(d, tile + d.TY, k, IN_N);
+                if ((k = s_kmin[2]) != INF_BITS && hw) activate(d, tile - 1, k, IN_E);
+                if ((k = s_kmin[3]) != INF_BITS && he) activate(d, tile + 1, k, IN_W);
+                if ((k = s_kmin[4]) != INF_BITS && hn && hw) activate(d, tile - d.TY - 1, k, IN_SE);
+                if ((k = s_kmin[5]) != INF_BITS && hn && he) activate(d, tile - d.TY + 1, k, IN_SW);
+                if ((k = s_kmin[6]) != INF_BITS && hs && hw) activate(d, tile + d.TY - 1, k, IN_NE);
+                if ((k = s_kmin[7]) != INF_BITS && hs && he) activate(d, tile + d.TY + 1, k, IN_NW);
                 for (int j = 0; j < 8; ++j) s_kmin[j] = INF_BITS;
                 // leave the tile, unless a neighbour changed our halo meanwhile
                 int again_f = 0;
@@ -379,9 +450,11 @@ __global__ void __launch_bounds__(NTHREADS) solver_kernel(GridDesc d) {
                 if (old != ST_RUN) {  // RUN|DIRTY
                     const int kk = atomicMin(&d.key[tile], INF_BITS);  // atomic read
                     if (kk < cur_thr_bits(d) || kk == INF_BITS) {
-                        // due now (or key lost to the reset race): keep the tile and go round again
-                        atomicExch(&d.key[tile], INF_BITS);
+                        // due now (or its key was consumed with the previous staging): go round again
                         atomicExch(&d.state[tile], ST_RUN);
+                        __threadfence();
+                        s_inmask = atomicExch(&d.inmask[tile], 0);
+                        atomicExch(&d.key[tile], INF_BITS);
                         __threadfence();
                         again_f = 1;
                     } else {
@@ -420,11 +493,14 @@ __global__ void __launch_bounds__(NTHREADS) solver_kernel(GridDesc d) {
     }
 
     // per-CTA counters -> global statistics
-    n_changed = __reduce_add_sync(0xffffffffu, (unsigned) n_changed);
+    for (int o = 16; o > 0; o >>= 1) {
+        n_changed += __shfl_down_sync(0xffffffffu, n_changed, o);
+    }
     if (lane == 0 && n_changed) atomicAdd(MODE == 0 ? &d.ctl->lowered : &d.ctl->invalidated, n_changed);
+    if (lane == 0 && n_evals) atomicAdd(&d.ctl->evals, n_evals);
     if (tid == 0) {
         atomicAdd(&d.ctl->visits, n_visits);
-        atomicAdd(&d.ctl->rounds, n_rounds);
+        atomicAdd(&d.ctl->rounds, n_iters);
     }
 }
 
@@ -452,6 +528,7 @@ __global__ void enqueue_seeds_kernel(GridDesc d) {
     for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < n; t += gridDim.x * blockDim.x) {
         if (d.seed[t]) {
             d.seed[t] = 0;
+            d.inmask[t] = 0x1ff;  // every element of a seeded tile is evaluated
             if (atomicOr(&d.state[t], ST_DIRTY) == 0) {
                 atomicAdd(&d.ctl->pending, 1);
                 unsigned long long s = atomicAdd(&d.ctl->tail, 1ULL);

@@ -136,6 +136,10 @@ def _ref_lib(kind):
         R.ref_extract.restype = C.c_int
         R.ref_extract.argtypes = [C.c_void_p, C.c_int, _f32p, C.c_int, C.c_int, C.c_int, _f32p, C.c_int, _f32p,
                                   _f32p, _f32p]
+        R.ref_op_tri.restype = C.c_float
+        R.ref_op_tri.argtypes = [C.c_void_p] + [C.c_int] * 6 + [C.c_float] * 2
+        R.ref_op_stencil.restype = C.c_float
+        R.ref_op_stencil.argtypes = [C.c_void_p] + [C.c_float] * 4
         _ref_libs[kind] = R
     return _ref_libs[kind]
 
@@ -205,6 +209,14 @@ class RefPlanner:
         rhs = np.empty(shape, np.float32)
         self.R.ref_dump(self.h, _p(g, _f32p), _p(rhs, _f32p))
         return g, rhs
+
+    def op_tri(self, n, pa, pb, ga, gb):
+        """compute_optimal_cost(n, p_a, p_b, g_a, g_b) of the FD*/MFD* planner on its current map."""
+        return self.R.ref_op_tri(self.h, n[0], n[1], pa[0], pa[1], pb[0], pb[1], ga, gb)
+
+    def op_stencil(self, ga, gb, tau, h):
+        """Value part of DFMPlanner::compute_optimal_cost."""
+        return self.R.ref_op_stencil(self.h, ga, gb, tau, h)
 
     def closed_mask(self):
         """Elements the reference settled: g == rhs < INF and g <= top key."""

@@ -21,6 +21,23 @@
 #include <chrono>
 #include <tuple>
 
+// Operator-level taps (ref_op_*) call the planners' private compute_optimal_cost: open the access
+// specifiers for THIS translation unit only, after every standard header the reference pulls in has been
+// included (so the library headers are untouched); the reference sources themselves stay unmodified.
+#include <algorithm>
+#include <array>
+#include <cassert>
+#include <functional>
+#include <map>
+#include <numeric>
+#include <queue>
+#include <set>
+#include <string>
+#include <unordered_map>
+#include <unordered_set>
+#include <utility>
+#define private public
+#define protected public
 #if defined(REF_FAMILY_FD)
 #include "FieldDPlanner.h"
 template<int O> using PlannerT = FieldDPlanner<O>;
@@ -60,6 +77,8 @@ struct IRef {
                         int allow_indirect, float *xy, int cap, float *cost, float *dist,
                         float *e_ms) = 0;
     virtual const uint8_t *map_bytes() = 0;
+    virtual float op_tri(int nx, int ny, int ax, int ay, int bx, int by, float ga, float gb) = 0;
+    virtual float op_stencil(float ga, float gb, float tau, float h) = 0;
 };
 
 template<int O>
@@ -148,6 +167,24 @@ struct Ref : IRef {
         return n;
     }
     const uint8_t *map_bytes() override { return data.get(); }
+    // the planner's own local update on caller-given neighbour values (costs come from the planner's map)
+    float op_tri(int nx, int ny, int ax, int ay, int bx, int by, float ga, float gb) override {
+#if defined(REF_FAMILY_DFM)
+        (void) nx; (void) ny; (void) ax; (void) ay; (void) bx; (void) by; (void) ga; (void) gb;
+        return std::numeric_limits<float>::quiet_NaN();
+#else
+        return planner.compute_optimal_cost(Node(nx, ny), Node(ax, ay), Node(bx, by), ga, gb);
+#endif
+    }
+    float op_stencil(float ga, float gb, float tau, float h) override {
+#if defined(REF_FAMILY_DFM)
+        Cell ca(0, 0), cb(1, 1);
+        return planner.compute_optimal_cost(ca, cb, ga, gb, tau, h).first;
+#else
+        (void) ga; (void) gb; (void) tau; (void) h;
+        return std::numeric_limits<float>::quiet_NaN();
+#endif
+    }
 };
 
 }  // namespace
@@ -183,6 +220,12 @@ int ref_extract(void *h, int use_field, const float *field, int max_steps, int l
                 float *xy, int cap, float *cost, float *dist, float *e_ms) {
     return static_cast<IRef *>(h)->extract(use_field, field, max_steps, lookahead, allow_indirect, xy, cap, cost,
                                            dist, e_ms);
+}
+float ref_op_tri(void *h, int nx, int ny, int ax, int ay, int bx, int by, float ga, float gb) {
+    return static_cast<IRef *>(h)->op_tri(nx, ny, ax, ay, bx, by, ga, gb);
+}
+float ref_op_stencil(void *h, float ga, float gb, float tau, float hh) {
+    return static_cast<IRef *>(h)->op_stencil(ga, gb, tau, hh);
 }
 const uint8_t *ref_map_bytes(void *h) { return static_cast<IRef *>(h)->map_bytes(); }
 

@@ -42,10 +42,17 @@ def build(force=False, verbose=False):
         cmd = [_nvcc()] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + [
             "-o", LIB, os.path.join(CSRC, "tasi_capi.cu")]
         subprocess.check_call(cmd)
+    build_hostops(force)
+    return LIB
+
+
+def build_hostops(force=False):
+    """The local updates of csrc/tasi_update.cuh compiled for the host (operator-level tests only)."""
+    srcs = [os.path.join(CSRC, "tasi_hostops.cpp"), os.path.join(CSRC, "tasi_update.cuh")]
     if force or _stale(HOSTLIB, srcs):
         subprocess.check_call(["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-fPIC", "-shared", "-o", HOSTLIB,
                                os.path.join(CSRC, "tasi_hostops.cpp")])
-    return LIB
+    return HOSTLIB
 
 
 if __name__ == "__main__":

@@ -55,6 +55,7 @@ typedef struct tasi_stats {
     float kernel_ms_solve;     /* CUDA-event time of the solver kernel(s), re-propagation phase */
     float kernel_ms_inval;     /* CUDA-event time of the invalidate phase */
     float kernel_ms_init;      /* field fill / seeding kernels */
+    float step_ms_device;      /* CUDA-event time of the whole step() on the planner's stream */
     int32_t solver_blocks;     /* persistent CTAs launched */
     int32_t solver_launches;   /* kernels launched by the last step() */
 } tasi_stats;

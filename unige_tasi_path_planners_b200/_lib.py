@@ -29,7 +29,8 @@ class Stats(C.Structure):
                 ("elem_lowered", C.c_uint64), ("queue_pushes", C.c_uint64), ("inval_visits", C.c_uint64),
                 ("elem_invalidated", C.c_uint64), ("seed_elems", C.c_uint64), ("phases", C.c_uint64),
                 ("far_parked", C.c_uint64), ("kernel_ms_solve", C.c_float),
-                ("kernel_ms_inval", C.c_float), ("kernel_ms_init", C.c_float), ("solver_blocks", C.c_int32),
+                ("kernel_ms_inval", C.c_float), ("kernel_ms_init", C.c_float), ("step_ms_device", C.c_float),
+                ("solver_blocks", C.c_int32),
                 ("solver_launches", C.c_int32)]
 
     def as_dict(self):

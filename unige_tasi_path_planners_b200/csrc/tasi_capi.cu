@@ -20,7 +20,7 @@ using namespace tasi;
 struct tasi_planner {
     int kind = TASI_FD, level = 0, device = 0;
     cudaStream_t stream = nullptr;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, evs0 = nullptr, evs1 = nullptr;
     int num_sms = 0;
 
     // the reference's flags (ReplannerBase.h:144-152)
@@ -290,6 +290,7 @@ int tasi_create(int kind, int level, int device, tasi_planner **out) {
     p->num_sms = prop.multiProcessorCount;
     if (cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking) != cudaSuccess ||
         cudaEventCreate(&p->ev0) != cudaSuccess || cudaEventCreate(&p->ev1) != cudaSuccess ||
+        cudaEventCreate(&p->evs0) != cudaSuccess || cudaEventCreate(&p->evs1) != cudaSuccess ||
         cudaMalloc(&p->ctl, sizeof(DevCtl)) != cudaSuccess ||
         cudaMemset(p->ctl, 0, sizeof(DevCtl)) != cudaSuccess) {
         tasi_destroy(p);
@@ -312,6 +313,8 @@ int tasi_destroy(tasi_planner *p) {
     cudaFree(p->ctl); cudaFree(p->cost_sum); cudaFree(p->patch_buf); cudaFree(p->chg_buf);
     if (p->ev0) cudaEventDestroy(p->ev0);
     if (p->ev1) cudaEventDestroy(p->ev1);
+    if (p->evs0) cudaEventDestroy(p->evs0);
+    if (p->evs1) cudaEventDestroy(p->evs1);
     if (p->stream) cudaStreamDestroy(p->stream);
     delete p;
     return TASI_OK;
@@ -455,6 +458,7 @@ int tasi_step(tasi_planner *p, float *u_ms, float *p_ms, uint64_t *n_updated, ui
     int rc;
     float ms = 0;
 
+    CU_TRY(p, cudaEventRecord(p->evs0, p->stream));
     double t0 = now_ms();
     if (p->initialize_search || p->new_goal) {  // ReplannerBase.h:48-55
         p->num_nodes_updated = 0;
@@ -499,6 +503,9 @@ int tasi_step(tasi_planner *p, float *u_ms, float *p_ms, uint64_t *n_updated, ui
         p->num_nodes_expanded = 0;
     }
     p->new_goal = p->initialize_search = false;
+    CU_TRY(p, cudaEventRecord(p->evs1, p->stream));
+    CU_TRY(p, cudaEventSynchronize(p->evs1));
+    CU_TRY(p, cudaEventElapsedTime(&p->stats.step_ms_device, p->evs0, p->evs1));
     double t2 = now_ms();
 
     if (u_ms) *u_ms = (float) (t1 - t0);

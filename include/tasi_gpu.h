@@ -58,6 +58,9 @@ typedef struct tasi_stats {
     float step_ms_device;      /* CUDA-event time of the whole step() on the planner's stream */
     int32_t solver_blocks;     /* persistent CTAs launched */
     int32_t solver_launches;   /* kernels launched by the last step() */
+    /* where the persistent CTAs spent their time in the solve phase (SM cycles summed over CTAs): waiting for a
+     * tile, staging it, relaxing it, writing back + activating neighbours */
+    uint64_t cyc_pop, cyc_stage, cyc_relax, cyc_post;
 } tasi_stats;
 
 /* Planner object. kind = TASI_FD|TASI_DFM|TASI_MFD; level = the reference's OPT_LVL template argument

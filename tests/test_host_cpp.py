@@ -1,0 +1,117 @@
+"""The C++ host side (unige_tasi_path_planners_b200/host/GpuPlanners.h): the planner classes with the
+reference's ReplannerBase surface, over the C ABI.
+
+CPU part: the classes compile stand-alone and fail loudly without a device. GPU part: host/plan_demo (plan +
+patch + replan through the classes) gives the oracle's field; oracle/_ref/ref_dropin_* (built in the build
+container from the reference's sources, travels as a binary) runs the UNMODIFIED reference extractor and demo
+loop over the GPU planner classes and over the reference's CPU planner side by side.
+"""
+import json
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from unige_tasi_path_planners_b200 import build, synth
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+KINDS = {"fd": 0, "dfm": 1, "mfd": 2}
+DROPIN = {"fd": "ref_dropin_fd", "dfm": "ref_dropin_dfm", "mfd": "ref_dropin_sg"}
+
+
+def _has_gpu():
+    try:
+        import torch
+        return torch.cuda.is_available()
+    except Exception:
+        return False
+
+
+@pytest.fixture(scope="module")
+def demo():
+    build.build()
+    return build.build_host_demo()
+
+
+def test_host_classes_compile_and_link(demo):
+    assert os.access(demo, os.X_OK)
+    r = subprocess.run([demo], capture_output=True, text=True)
+    assert r.returncode == 64 and "usage" in r.stderr
+
+
+def test_host_classes_have_no_cpu_fallback(demo):
+    if _has_gpu():
+        pytest.skip("a CUDA device is present")
+    r = subprocess.run([demo, "fd", "1", "32", "32", "1"], capture_output=True, text=True)
+    assert r.returncode == 70
+    assert "no CPU fallback" in r.stderr
+
+
+def test_header_mirrors_the_reference_surface():
+    """Every public member of ReplannerBase (ReplannerBase.h:39-123, 144-156) the demos touch exists by name."""
+    src = open(os.path.join(ROOT, "unige_tasi_path_planners_b200", "host", "GpuPlanners.h")).read()
+    for name in ["void reset()", "int step()", "void set_occupancy_threshold(float", "void set_heuristic_multiplier(float",
+                 "void set_map(const std::shared_ptr<uint8_t> &", "void patch_map(const std::shared_ptr<uint8_t> &",
+                 "void set_start(const Position &", "void set_goal(const Position &", "get_expanded_map()", "get_grid()",
+                 "u_time", "p_time", "num_nodes_updated", "num_nodes_expanded", "heuristic_multiplier",
+                 "initialize_graph", "initialize_search", "goal_set", "new_goal", "new_start",
+                 "class GpuFieldDPlanner", "class GpuDFMPlanner", "class GpuShiftedGridPlanner"]:
+        assert name in src, name
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("kind", ["fd", "dfm", "mfd"])
+def test_plan_demo_matches_oracle(demo, oracle, kind, tmp_path):
+    L, W, seed = 150, 210, 17
+    px, py, ph, pw, pseed = 40, 50, 30, 44, 99
+    dump = str(tmp_path / "f")
+    r = subprocess.run([demo, kind, "1", str(L), str(W), str(seed), "--patch", str(px), str(py), str(ph), str(pw),
+                        str(pseed), "--dump", dump], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    lines = [json.loads(l) for l in r.stdout.splitlines()]
+    assert [l["step"] for l in lines] == ["plan", "replan"]
+    k = KINDS[kind]
+    start, goal = (5.0, 5.0), (float(L - 6), float(W - 6))
+    cmap = synth.synth_map(seed, L, W, 10, start, goal)
+    shape = oracle.field_shape(k, L, W)
+    for what, cm in (("plan", cmap), ("replan", None)):
+        if cm is None:
+            cm = cmap.copy()
+            oracle.patch(cm, synth.synth_rows(pseed, 0, ph, pw, 15), px, py)
+        got = np.fromfile(dump + "." + what, np.float32).reshape(shape)
+        want = oracle.solve(k, cm, goal)
+        assert np.array_equal(np.isfinite(got), np.isfinite(want))
+        m = np.isfinite(want)
+        if k == 1:
+            assert (np.abs(got[m] - want[m]) / np.maximum(want[m], 1e-30)).max() <= 1e-4
+        else:
+            assert np.array_equal(got[m], want[m])
+    assert lines[1]["num_nodes_updated"] > 0 and lines[0]["tile_visits"] > 0
+    # FieldMap hand-off: get_rhs(start element) is the field value there
+    ex = (5, 5)
+    assert lines[0]["start_value"] == pytest.approx(float(np.fromfile(dump + ".plan", np.float32).reshape(shape)[ex]))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("kind,level", [("fd", 1), ("fd", 0), ("mfd", 1), ("dfm", 1)])
+def test_reference_extractor_and_demo_loop_over_gpu_planner(kind, level):
+    """The reference's own extractor + demo loop: CPU planner vs GPU planner class, same patches, step by step."""
+    exe = os.path.join(ROOT, "oracle", "_ref", DROPIN[kind])
+    if not os.access(exe, os.X_OK):
+        pytest.skip("oracle/_ref drop-in binaries not built (the reference sources are absent)")
+    r = subprocess.run([exe, str(level), "96", "120", "5", "40", "6"], capture_output=True, text=True, timeout=600)
+    lines = [json.loads(l) for l in r.stdout.splitlines() if l.startswith("{")]
+    assert lines, r.stderr
+    steps = [l for l in lines if "iter" in l]
+    assert len(steps) >= 5
+    if kind == "dfm":
+        # MS-DFM fields agree to ~1e-7, not bit for bit: path cost within 1e-3 (north_star), points within 1e-3 cell
+        for s in steps:
+            assert s["ref_points"] == s["gpu_points"]
+            assert s["max_point_diff"] <= 1e-3
+            assert abs(s["ref_cost"] - s["gpu_cost"]) <= 1e-3 * abs(s["ref_cost"])
+    else:
+        assert r.returncode == 0, r.stdout[-2000:]
+        assert all(s["identical"] for s in steps)
+        assert lines[-1]["mismatching_steps"] == 0

@@ -31,7 +31,9 @@ class Stats(C.Structure):
                 ("far_parked", C.c_uint64), ("kernel_ms_solve", C.c_float),
                 ("kernel_ms_inval", C.c_float), ("kernel_ms_init", C.c_float), ("step_ms_device", C.c_float),
                 ("solver_blocks", C.c_int32),
-                ("solver_launches", C.c_int32)]
+                ("solver_launches", C.c_int32),
+                ("cyc_pop", C.c_uint64), ("cyc_stage", C.c_uint64), ("cyc_relax", C.c_uint64),
+                ("cyc_post", C.c_uint64)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}

@@ -55,7 +55,23 @@ def build_hostops(force=False):
     return HOSTLIB
 
 
+HOST_DIR = os.path.join(PKG, "host")
+HOST_DEMO = os.path.join(HOST_DIR, "plan_demo")
+
+
+def build_host_demo(force=False):
+    """The C++ host classes (host/GpuPlanners.h) exercised by host/plan_demo.cpp, linked against libtasi_gpu.so."""
+    srcs = [os.path.join(HOST_DIR, "plan_demo.cpp"), os.path.join(HOST_DIR, "GpuPlanners.h"),
+            os.path.join(PKG, "..", "include", "tasi_gpu.h"), LIB]
+    if force or _stale(HOST_DEMO, srcs):
+        subprocess.check_call(["g++", "-std=c++17", "-O2", "-Wall", "-I", os.path.join(PKG, "..", "include"), "-I", HOST_DIR,
+                               os.path.join(HOST_DIR, "plan_demo.cpp"), "-L", PKG, "-ltasi_gpu",
+                               "-Wl,-rpath,$ORIGIN/..", "-o", HOST_DEMO])
+    return HOST_DEMO
+
+
 if __name__ == "__main__":
     import sys
     build(force="--force" in sys.argv, verbose="-v" in sys.argv)
+    build_host_demo(force="--force" in sys.argv)
     print(LIB)

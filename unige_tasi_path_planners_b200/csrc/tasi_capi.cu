@@ -44,12 +44,12 @@ struct tasi_planner {
     int64_t gpitch = 0, cpitch = 0, g_rows = 0;
     int *state = nullptr, *queue = nullptr;
     uint8_t *seed = nullptr;
-    int *key = nullptr, *far = nullptr, *inmask = nullptr;
+    int *key = nullptr, *far = nullptr;
     int far_cap = 0;
     unsigned long long *cost_sum = nullptr;  // device: {sum of free-cell costs, number of free cells}
     bool cost_stats_valid = false;
     float mean_cost = 1.0f;
-    float delta_factor = 0.5f;
+    float delta_factor = 2.0f;
     DevCtl *ctl = nullptr;
     float *stage = nullptr;  // 2 x EY receive rows (band mode)
     uint8_t *patch_buf = nullptr, *chg_buf = nullptr;
@@ -98,7 +98,7 @@ GridDesc make_desc(const tasi_planner *p) {
     d.pin_x = (int) px; d.pin_y = (int) py;
     d.state = p->state; d.queue = p->queue; d.qmask = p->qsize - 1;
     d.seed = p->seed; d.ctl = p->ctl;
-    d.inmask = p->inmask; d.key = p->key; d.far = p->far; d.far_cap = p->far_cap;
+    d.key = p->key; d.far = p->far; d.far_cap = p->far_cap;
     d.delta = p->delta_factor * (float) TS * p->mean_cost;
     d.inval_tol = (p->kind == TASI_DFM) ? 1e-6f : 0.0f;
     return d;
@@ -106,8 +106,8 @@ GridDesc make_desc(const tasi_planner *p) {
 
 void free_grid(tasi_planner *p) {
     cudaFree(p->g_base); cudaFree(p->c_base); cudaFree(p->state); cudaFree(p->queue); cudaFree(p->seed);
-    cudaFree(p->stage); cudaFree(p->key); cudaFree(p->far); cudaFree(p->inmask);
-    p->key = nullptr; p->far = nullptr; p->inmask = nullptr;
+    cudaFree(p->stage); cudaFree(p->key); cudaFree(p->far);
+    p->key = nullptr; p->far = nullptr;
     p->g_base = nullptr; p->c_base = nullptr; p->state = nullptr; p->queue = nullptr; p->seed = nullptr;
     p->stage = nullptr;
 }
@@ -163,8 +163,6 @@ int alloc_grid(tasi_planner *p, int W, int rows) {
     p->far_cap = 2 * nt + 64;
     CU_TRY(p, cudaMalloc(&p->key, sizeof(int) * (size_t) ((nt + 3) / 4 * 4)));
     CU_TRY(p, cudaMalloc(&p->far, sizeof(int) * 2 * (size_t) p->far_cap));
-    CU_TRY(p, cudaMalloc(&p->inmask, sizeof(int) * nt));
-    CU_TRY(p, cudaMemsetAsync(p->inmask, 0, sizeof(int) * nt, p->stream));
     CU_TRY(p, cudaMalloc(&p->stage, sizeof(float) * 2 * (size_t) EY));
     CU_TRY(p, cudaMemsetAsync(p->c_base, 255, (size_t) p->cpitch * p->g_rows, p->stream));
     CU_TRY(p, cudaMemsetAsync(p->state, 0, sizeof(int) * nt, p->stream));
@@ -236,6 +234,8 @@ int run_solver(tasi_planner *p, int mode, float *ms) {
         p->stats.tile_rounds += h.rounds;
         p->stats.elem_lowered += h.lowered;
         p->stats.elem_evals += h.evals;
+        p->stats.cyc_pop += h.cyc_pop; p->stats.cyc_stage += h.cyc_stage;
+        p->stats.cyc_relax += h.cyc_relax; p->stats.cyc_post += h.cyc_post;
     } else {
         p->stats.inval_visits += h.visits;
         p->stats.elem_invalidated += h.invalidated;
@@ -257,7 +257,6 @@ int init_field(tasi_planner *p) {
     const int nt = p->TX * p->TY;
     CU_TRY(p, cudaMemsetAsync(p->seed, 0, nt, p->stream));
     CU_TRY(p, cudaMemsetAsync(p->state, 0, sizeof(int) * nt, p->stream));
-    CU_TRY(p, cudaMemsetAsync(p->inmask, 0, sizeof(int) * nt, p->stream));
     const int64_t n4 = p->gpitch * p->g_rows / 4;
     fill_inf_kernel<<<p->num_sms * 8, 256, 0, p->stream>>>((float4 *) p->g_base, n4);
     fill_inf_kernel<<<64, 256, 0, p->stream>>>((float4 *) p->key, (nt + 3) / 4);

@@ -33,6 +33,8 @@ constexpr int NTHREADS = 128;  // 4 warps = 4 sweep directions
 constexpr int ST_DIRTY = 1;
 constexpr int ST_RUN = 2;
 constexpr int ST_FAR = 4;      // queued, but parked in the far pile (key >= current threshold)
+constexpr int ST_MASK = 7;     // the three state bits; bits ST_SHIFT.. of the same word hold the IN_* direction
+constexpr int ST_SHIFT = 8;    // bits (which halo sides changed since the tile was last staged)
 constexpr int INF_BITS = 0x7f800000;
 constexpr int GMARGIN = 32;    // columns of margin left of element/cell column 0 (keeps rows 128B aligned)
 
@@ -49,6 +51,7 @@ struct DevCtl {
     int phases;                     // threshold advances
     unsigned long long far_parked;  // activations that went to the far pile
     unsigned long long evals;       // element evaluations
+    unsigned long long cyc_pop, cyc_stage, cyc_relax, cyc_post;  // SM cycles summed over CTAs (thread 0's clock)
     // patch bookkeeping
     unsigned long long n_changed, n_raised, n_lowered_cells, n_seed_elems;
     unsigned long long halo_lowered;
@@ -68,7 +71,6 @@ struct GridDesc {
     int *queue;            // ring of tile id + 1, 0 = empty
     unsigned qmask;        // ring size - 1
     uint8_t *seed;         // TX*TY: tiles to enqueue before the next solver launch
-    int *inmask;           // TX*TY: IN_* bits, which halo sides changed since the tile was last staged
     int *key;              // TX*TY: float bits of the lowest value that entered the tile since its last visit
     int *far;              // 2 * far_cap tile ids: the far pile, double-buffered
     int far_cap;
@@ -144,23 +146,21 @@ __device__ inline void far_append(const GridDesc &d, int tile) {
 }
 
 __device__ inline void activate(const GridDesc &d, int tile, int kbits, int dirbit) {
-    atomicOr(&d.inmask[tile], dirbit);
     atomicMin(&d.key[tile], kbits);
-    __threadfence();  // mask and key must be in place before the state says "queued"
+    __threadfence();  // the key must be in place before the state says "queued"
     const bool near = kbits < cur_thr_bits(d);
-    int old = atomicCAS(&d.state[tile], 0, near ? ST_DIRTY : (ST_DIRTY | ST_FAR));
-    if (old != 0) {
-        old = atomicOr(&d.state[tile], ST_DIRTY);
-        if (old == 0 && !near) atomicOr(&d.state[tile], ST_FAR);  // it went idle in between: ours to queue
-    }
-    if (old == 0) {
+    // one atomic both flags the tile and records which of its halo sides changed (bits ST_SHIFT..)
+    const int old = atomicOr(&d.state[tile], ST_DIRTY | (dirbit << ST_SHIFT));
+    const int st = old & ST_MASK;
+    if (st == 0) {  // it was idle: ours to queue
         if (near) {
             q_push(d, tile);
             atomicAdd(&d.ctl->pushes, 1ULL);
         } else {
+            atomicOr(&d.state[tile], ST_FAR);
             far_append(d, tile);
         }
-    } else if ((old & ST_FAR) && near) {
+    } else if ((st & ST_FAR) && near) {
         // parked with a higher key: promote (whoever clears ST_FAR owns the push; the pile entry goes stale)
         if (atomicAnd(&d.state[tile], ~ST_FAR) & ST_FAR) {
             q_push(d, tile);
@@ -332,8 +332,18 @@ __device__ __forceinline__ int relax_tile(float *sg, const float *sc, unsigned *
 }
 
 // ---- the persistent solver kernel ------------------------------------------------------------------------------
+// Staging geometry: values are fetched as 16-byte vectors from column y0-4 (rows are 128-byte aligned and the
+// arrays carry GMARGIN columns of margin), 10 vectors cover columns y0-4..y0+35 of one row; costs likewise as
+// 4-byte vectors. Every thread issues all of its loads before the first use, so a tile is staged in about one
+// L2 round trip.
+constexpr int GV_PER_ROW = 10;
+constexpr int G_VECS = (TS + 2) * GV_PER_ROW;                                  // 340 float4 per tile
+constexpr int G_ITERS = (G_VECS + NTHREADS - 1) / NTHREADS;                    // 3
+constexpr int C_ROWS_NODE = TS + 1, C_ROWS_CELL = TS;
+constexpr int C_ITERS = (C_ROWS_NODE * GV_PER_ROW + NTHREADS - 1) / NTHREADS;  // 3
+
 template <int KIND, int MODE>
-__global__ void __launch_bounds__(NTHREADS) solver_kernel(GridDesc d) {
+__global__ void __launch_bounds__(NTHREADS, 8) solver_kernel(GridDesc d) {
     __shared__ float sg[(TS + 2) * GP];   // values, rows/cols -1..32
     __shared__ float sc[(TS + 1) * CP];   // cell costs as float, INF = obstacle
     __shared__ unsigned s_dirty[TS], s_chg[TS];
@@ -345,16 +355,18 @@ __global__ void __launch_bounds__(NTHREADS) solver_kernel(GridDesc d) {
     const float INF = __int_as_float(0x7f800000);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     unsigned long long n_visits = 0, n_iters = 0, n_changed = 0, n_evals = 0;
+    long long c_pop = 0, c_stage = 0, c_relax = 0, c_post = 0, c0 = clock64(), c1;
 
     for (;;) {
         if (tid == 0) {
             int t = q_pop(d);
             if (t >= 0) {
-                atomicExch(&d.state[t], ST_RUN);  // clears DIRTY; activations ordered before it are consumed below
-                __threadfence();
-                s_inmask = atomicExch(&d.inmask[t], 0);
+                // claim the tile: the word we take away carries the direction bits of every activation so far;
+                // their values were fenced before the bits were set, the fence below orders our loads after it
+                const int old = atomicExch(&d.state[t], ST_RUN);
+                s_inmask = old >> ST_SHIFT;
                 atomicExch(&d.key[t], INF_BITS);
-                __threadfence();                  // ... and their values are visible to the loads below
+                __threadfence();
             }
             s_tile = t;
         }
@@ -362,33 +374,66 @@ __global__ void __launch_bounds__(NTHREADS) solver_kernel(GridDesc d) {
         __syncthreads();
         const int tile = s_tile;
         if (tile < 0) break;
+        c1 = clock64(); c_pop += c1 - c0; c0 = c1;
         const int tx = tile / d.TY, ty = tile - tx * d.TY;
         const int x0 = tx * TS, y0 = ty * TS;
         const int rlim = min(TS, d.EX - x0), clim = min(TS, d.EY - y0);
         const unsigned colmask = clim >= 32 ? 0xffffffffu : ((1u << clim) - 1u);
         const int pin_r = d.pin_x - x0, pin_c = d.pin_y - y0;
 
-        // cell costs around the tile (immutable while the solver runs)
-        if (KIND == TASI_KIND_DFM) {
-            for (int i = tid; i < TS * TS; i += NTHREADS) {
-                const int r = i >> 5, c = i & 31;
-                const uint8_t b = __ldg(d.cost + (int64_t) (x0 + r) * d.cpitch + (y0 + c));
-                sc[r * CP + c] = (b >= d.thr) ? INF : (float) b;
-            }
-        } else {
-            for (int i = tid; i < (TS + 1) * (TS + 1); i += NTHREADS) {
-                const int r = i / (TS + 1), c = i - r * (TS + 1);
-                const uint8_t b = __ldg(d.cost + (int64_t) (x0 - 1 + r) * d.cpitch + (y0 - 1 + c));
-                sc[r * CP + c] = (b >= d.thr) ? INF : (float) b;
-            }
+        // cell costs around the tile (immutable while the solver runs): issue the loads now, convert after the
+        // value loads of the first staging are in flight too
+        constexpr int c_r0 = (KIND == TASI_KIND_DFM) ? 0 : -1;  // first cost row / column relative to the tile
+        constexpr int c_rows = (KIND == TASI_KIND_DFM) ? C_ROWS_CELL : C_ROWS_NODE;
+        uchar4 cv[C_ITERS];
+#pragma unroll
+        for (int k = 0; k < C_ITERS; ++k) {
+            const int i = tid + k * NTHREADS;
+            const int r = i / GV_PER_ROW, v = i - r * GV_PER_ROW;
+            if (i < c_rows * GV_PER_ROW)
+                cv[k] = __ldg((const uchar4 *) (d.cost + (int64_t) (x0 + c_r0 + r) * d.cpitch + (y0 - 4 + 4 * v)));
         }
+        bool first = true;
 
         bool again;
         do {
             // stage values + halo ring; L1 is bypassed (other CTAs write these lines)
-            for (int i = tid; i < (TS + 2) * (TS + 2); i += NTHREADS) {
-                const int r = i / (TS + 2), c = i - r * (TS + 2);
-                sg[r * GP + c] = __ldcg(d.g + (int64_t) (x0 - 1 + r) * d.gpitch + (y0 - 1 + c));
+            float4 gv[G_ITERS];
+#pragma unroll
+            for (int k = 0; k < G_ITERS; ++k) {
+                const int i = tid + k * NTHREADS;
+                const int r = i / GV_PER_ROW, v = i - r * GV_PER_ROW;
+                if (i < G_VECS)
+                    gv[k] = __ldcg((const float4 *) (d.g + (int64_t) (x0 - 1 + r) * d.gpitch + (y0 - 4 + 4 * v)));
+            }
+            if (first) {
+                first = false;
+#pragma unroll
+                for (int k = 0; k < C_ITERS; ++k) {
+                    const int i = tid + k * NTHREADS;
+                    const int r = i / GV_PER_ROW, v = i - r * GV_PER_ROW;
+                    if (i < c_rows * GV_PER_ROW) {
+                        const unsigned char bb[4] = {cv[k].x, cv[k].y, cv[k].z, cv[k].w};
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            const int c = 4 * v + e - 4 - c_r0;  // column index inside sc
+                            if (c >= 0 && c < c_rows) sc[r * CP + c] = (bb[e] >= d.thr) ? INF : (float) bb[e];
+                        }
+                    }
+                }
+            }
+#pragma unroll
+            for (int k = 0; k < G_ITERS; ++k) {
+                const int i = tid + k * NTHREADS;
+                const int r = i / GV_PER_ROW, v = i - r * GV_PER_ROW;
+                if (i < G_VECS) {
+                    const float ff[4] = {gv[k].x, gv[k].y, gv[k].z, gv[k].w};
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        const int c = 4 * v + e - 3;  // sg column: element column y0-1 is column 0
+                        if (c >= 0 && c < TS + 2) sg[r * GP + c] = ff[e];
+                    }
+                }
             }
             if (tid < TS) {
                 s_dirty[tid] = initial_dirty(s_inmask, tid, rlim, colmask);
@@ -396,12 +441,14 @@ __global__ void __launch_bounds__(NTHREADS) solver_kernel(GridDesc d) {
             }
             __syncthreads();
             ++n_visits;
+            c1 = clock64(); c_stage += c1 - c0; c0 = c1;
 
             unsigned it = 0, ev = 0;
             n_changed += relax_tile<KIND, MODE>(sg, sc, s_dirty, s_chg, s_list[warp], warp, lane, rlim, clim, pin_r,
                                                 pin_c, d.inval_tol, it, ev);
             n_iters += it;
             n_evals += ev;
+            c1 = clock64(); c_relax += c1 - c0; c0 = c1;
 
             // write back what changed; per neighbour direction keep the lowest changed value it reads
             {
@@ -430,35 +477,36 @@ __global__ void __launch_bounds__(NTHREADS) solver_kernel(GridDesc d) {
             __threadfence();
             __syncthreads();
 
+            // activate the neighbours that read a changed border, one thread per direction
+            // (0 N, 1 S, 2 W, 3 E, 4 NW, 5 NE, 6 SW, 7 SE); our north border is the south halo of the tile above
+            if (tid < 8) {
+                const int k = s_kmin[tid];
+                s_kmin[tid] = INF_BITS;
+                const int dx = (0x31 >> tid & 1) ? -1 : ((0xc2 >> tid & 1) ? 1 : 0);
+                const int dy = (0x54 >> tid & 1) ? -1 : ((0xa8 >> tid & 1) ? 1 : 0);
+                const int seen_as = (IN_S << 0) * (tid == 0) + IN_N * (tid == 1) + IN_E * (tid == 2) + IN_W * (tid == 3) +
+                                    IN_SE * (tid == 4) + IN_SW * (tid == 5) + IN_NE * (tid == 6) + IN_NW * (tid == 7);
+                const int nx = tx + dx, ny = ty + dy;
+                if (k != INF_BITS && nx >= 0 && nx < d.TX && ny >= 0 && ny < d.TY) activate(d, nx * d.TY + ny, k, seen_as);
+            }
+            __syncthreads();
+
             if (tid == 0) {
                 if (MODE == 1) d.seed[tile] = 1;  // phase 2 revisits every tile phase 1 looked at
-                const bool hn = tx > 0, hs = tx + 1 < d.TX, hw = ty > 0, he = ty + 1 < d.TY;
-                int k;
-                // our north border is the south halo of the tile above, and so on
-                if ((k = s_kmin[0]) != INF_BITS && hn) activate(d, tile - d.TY, k, IN_S);
-                if ((k = s_kmin[1]) != INF_BITS && hs) activate(d, tile + d.TY, k, IN_N);
-                if ((k = s_kmin[2]) != INF_BITS && hw) activate(d, tile - 1, k, IN_E);
-                if ((k = s_kmin[3]) != INF_BITS && he) activate(d, tile + 1, k, IN_W);
-                if ((k = s_kmin[4]) != INF_BITS && hn && hw) activate(d, tile - d.TY - 1, k, IN_SE);
-                if ((k = s_kmin[5]) != INF_BITS && hn && he) activate(d, tile - d.TY + 1, k, IN_SW);
-                if ((k = s_kmin[6]) != INF_BITS && hs && hw) activate(d, tile + d.TY - 1, k, IN_NE);
-                if ((k = s_kmin[7]) != INF_BITS && hs && he) activate(d, tile + d.TY + 1, k, IN_NW);
-                for (int j = 0; j < 8; ++j) s_kmin[j] = INF_BITS;
                 // leave the tile, unless a neighbour changed our halo meanwhile
                 int again_f = 0;
                 int old = atomicCAS(&d.state[tile], ST_RUN, 0);
-                if (old != ST_RUN) {  // RUN|DIRTY
+                if (old != ST_RUN) {  // RUN|DIRTY + direction bits
                     const int kk = atomicMin(&d.key[tile], INF_BITS);  // atomic read
                     if (kk < cur_thr_bits(d) || kk == INF_BITS) {
                         // due now (or its key was consumed with the previous staging): go round again
-                        atomicExch(&d.state[tile], ST_RUN);
-                        __threadfence();
-                        s_inmask = atomicExch(&d.inmask[tile], 0);
+                        old = atomicExch(&d.state[tile], ST_RUN);
+                        s_inmask = old >> ST_SHIFT;
                         atomicExch(&d.key[tile], INF_BITS);
                         __threadfence();
                         again_f = 1;
                     } else {
-                        atomicExch(&d.state[tile], ST_DIRTY | ST_FAR);
+                        atomicXor(&d.state[tile], ST_RUN | ST_FAR);  // RUN|DIRTY -> DIRTY|FAR, direction bits stay
                         far_append(d, tile);
                     }
                 }
@@ -467,6 +515,7 @@ __global__ void __launch_bounds__(NTHREADS) solver_kernel(GridDesc d) {
             }
             __syncthreads();
             again = s_again != 0;
+            c1 = clock64(); c_post += c1 - c0; c0 = c1;
         } while (again);
 
         // the tile is no longer pending; whoever takes the count to 0 advances the threshold
@@ -501,6 +550,10 @@ __global__ void __launch_bounds__(NTHREADS) solver_kernel(GridDesc d) {
     if (tid == 0) {
         atomicAdd(&d.ctl->visits, n_visits);
         atomicAdd(&d.ctl->rounds, n_iters);
+        atomicAdd(&d.ctl->cyc_pop, (unsigned long long) c_pop);
+        atomicAdd(&d.ctl->cyc_stage, (unsigned long long) c_stage);
+        atomicAdd(&d.ctl->cyc_relax, (unsigned long long) c_relax);
+        atomicAdd(&d.ctl->cyc_post, (unsigned long long) c_post);
     }
 }
 
@@ -528,8 +581,8 @@ __global__ void enqueue_seeds_kernel(GridDesc d) {
     for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < n; t += gridDim.x * blockDim.x) {
         if (d.seed[t]) {
             d.seed[t] = 0;
-            d.inmask[t] = 0x1ff;  // every element of a seeded tile is evaluated
-            if (atomicOr(&d.state[t], ST_DIRTY) == 0) {
+            // every element of a seeded tile is evaluated (all direction bits)
+            if ((atomicOr(&d.state[t], ST_DIRTY | (0x1ff << ST_SHIFT)) & ST_MASK) == 0) {
                 atomicAdd(&d.ctl->pending, 1);
                 unsigned long long s = atomicAdd(&d.ctl->tail, 1ULL);
                 d.queue[(unsigned) s & d.qmask] = t + 1;

@@ -1,0 +1,281 @@
+"""Row-band sharding of one large grid across GPUs (BASELINE.json cfg4).
+
+The reference has no multi-device path; this is the sharded form of the same fixed-point solve.
+Band r owns a contiguous range of element rows plus one halo row of values on each open side. One outer
+iteration = every band drains its own tile queue (tasi_band_solve), neighbours swap their boundary rows
+(point-to-point send/recv: NCCL over NVLink on GPUs), each band merges the received row into its halo
+(tasi_band_import, which re-activates the border tiles whose halo got lower), and an all-reduce of the number of
+lowered halo values decides global convergence (0 everywhere = every band is at its fixed point with halos that
+agree with their owners, i.e. the single-grid fixed point, bit for bit).
+
+`run_bands` is the whole protocol and only needs a band object and a communicator, so the same code runs
+  * one process per GPU under torch.distributed (GpuBand + DistComm, backend nccl),
+  * all bands in one process on one GPU (GpuBand + LocalComm) — the single-GPU test of the band C ABI,
+  * on CPU tensors with the gloo backend (tests/ supplies a CPU band) — the world_size-2 test of the host logic.
+"""
+import numpy as np
+
+from . import planner as _planner
+
+
+def split_rows(n_rows, parts):
+    """Contiguous, near-equal split of element rows [0, n_rows) into `parts` ranges [(a, b), ...]."""
+    base, rem = divmod(n_rows, parts)
+    out, a = [], 0
+    for r in range(parts):
+        b = a + base + (1 if r < rem else 0)
+        out.append((a, b))
+        a = b
+    return out
+
+
+def band_geometry(kind, length, parts, r):
+    """Element rows [a, b) owned by band r of `parts`, and the cell rows [c0, c1) it must store.
+
+    Node planners (FD*, MFD*): the (length+1) node rows are split; updating node row x reads cell rows x-1 and x,
+    so an open top adds cell row a-1 and an open bottom keeps cell row b-1 (the cells under the last owned row).
+    MS-DFM: cell rows are split and a cell's update reads only its own cost."""
+    node = kind != _planner.DFM
+    n_elem_rows = length + 1 if node else length
+    a, b = split_rows(n_elem_rows, parts)[r]
+    open_top, open_bottom = r > 0, r < parts - 1
+    if node:
+        c0 = a - 1 if open_top else 0
+        c1 = b if open_bottom else length
+    else:
+        c0, c1 = a, b
+    return dict(a=a, b=b, c0=c0, c1=c1, open_top=open_top, open_bottom=open_bottom)
+
+
+class DistComm:
+    """torch.distributed point-to-point + all-reduce (nccl on GPUs, gloo on CPU tensors)."""
+
+    def __init__(self, dist, rank, world, device=None):
+        self.dist, self.rank, self.world, self.device = dist, rank, world, device
+
+    def exchange(self, band):
+        import torch
+        ops = []
+        for side, peer in ((0, self.rank - 1), (1, self.rank + 1)):
+            if 0 <= peer < self.world:
+                ops.append(self.dist.P2POp(self.dist.isend, band.send_row(side), peer))
+                ops.append(self.dist.P2POp(self.dist.irecv, band.recv_stage(side), peer))
+        if ops:
+            for w in self.dist.batch_isend_irecv(ops):
+                w.wait()
+            if self.device is not None:
+                torch.cuda.current_stream(self.device).synchronize()
+
+    def total(self, value):
+        import torch
+        t = torch.tensor([int(value)], dtype=torch.int64, device=self.device if self.device is not None else "cpu")
+        if self.world > 1:
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.SUM)
+        return int(t.item())
+
+
+def run_bands(band, comm, max_outer=1 << 20):
+    """Solve to global convergence. Returns the number of outer iterations (halo exchanges)."""
+    band.begin()
+    outer = 0
+    while True:
+        band.solve()
+        comm.exchange(band)
+        lowered = 0
+        if band.open_top:
+            lowered += band.import_side(0)
+        if band.open_bottom:
+            lowered += band.import_side(1)
+        outer += 1
+        if comm.total(lowered) == 0:
+            return outer
+        if outer >= max_outer:
+            raise RuntimeError("band solve did not converge in %d exchanges" % max_outer)
+
+
+def run_bands_local(bands, max_outer=1 << 20):
+    """All bands in this process (one GPU or CPU): same protocol, rows copied directly between neighbours."""
+    for b in bands:
+        b.begin()
+    outer = 0
+    while True:
+        for b in bands:
+            b.solve()
+        for r in range(len(bands) - 1):
+            bands[r + 1].recv_stage(0).copy_(bands[r].send_row(1))
+            bands[r].recv_stage(1).copy_(bands[r + 1].send_row(0))
+        _sync(bands)
+        lowered = 0
+        for b in bands:
+            if b.open_top:
+                lowered += b.import_side(0)
+            if b.open_bottom:
+                lowered += b.import_side(1)
+        outer += 1
+        if lowered == 0:
+            return outer
+        if outer >= max_outer:
+            raise RuntimeError("band solve did not converge in %d exchanges" % max_outer)
+
+
+def _sync(bands):
+    if bands and getattr(bands[0], "device", None) is not None:
+        import torch
+        torch.cuda.synchronize(bands[0].device)
+
+
+class _DevRow:
+    """CUDA-array-interface view of `n` float32 at device pointer `ptr` (so torch can wrap it without a copy)."""
+
+    def __init__(self, ptr, n):
+        self.__cuda_array_interface__ = {"shape": (int(n),), "typestr": "<f4", "data": (int(ptr), False), "version": 2}
+
+
+class GpuBand:
+    """One row band on one GPU over the band entry points of the C ABI (include/tasi_gpu.h)."""
+
+    def __init__(self, kind, level, length, width, parts, r, device=0):
+        import torch
+        self.kind, self.length, self.width, self.parts, self.r, self.device = kind, length, width, parts, r, device
+        geo = band_geometry(kind, length, parts, r)
+        self.geo = geo
+        self.open_top, self.open_bottom = geo["open_top"], geo["open_bottom"]
+        self.p = _planner.PLANNERS[kind](level, device=device)
+        self.p.band_config(geo["a"], self.open_top, self.open_bottom)
+        self._torch = torch
+        self._rows = {}
+
+    # -- map ------------------------------------------------------------------------------------------------
+    def set_map_from_global(self, cmap, occ=1.0):
+        self.p.set_occupancy_threshold(occ)
+        self.p.set_map(np.ascontiguousarray(cmap[self.geo["c0"]:self.geo["c1"]]))
+        self._bind()
+
+    def synth_map(self, seed, p_obs, start, goal, occ=1.0):
+        self.p.set_occupancy_threshold(occ)
+        g = self.geo
+        self.p.synth_map(seed, self.width, g["c1"] - g["c0"], row0=g["c0"], p_obs=p_obs, start=start, goal=goal)
+        self._bind()
+
+    def _bind(self):
+        self._rows = {}
+        for side in (0, 1):
+            s, rcv, n = self.p.band_rows(side)
+            dev = "cuda:%d" % self.device
+            self._rows[side] = (self._torch.as_tensor(_DevRow(s, n), device=dev),
+                                self._torch.as_tensor(_DevRow(rcv, n), device=dev))
+
+    def set_endpoints(self, start, goal):
+        self.p.set_start(*start)
+        self.p.set_goal(*goal)  # global coordinates; the band pins the goal only if it owns that row
+
+    # -- protocol ---------------------------------------------------------------------------------------------
+    def begin(self):
+        rc = self.p.band_begin()
+        assert rc == 0, rc
+
+    def solve(self):
+        return self.p.band_solve()
+
+    def send_row(self, side):
+        return self._rows[side][0]
+
+    def recv_stage(self, side):
+        return self._rows[side][1]
+
+    def import_side(self, side):
+        return self.p.band_import(side)
+
+    # -- results ----------------------------------------------------------------------------------------------
+    def read_owned(self):
+        return self.p.read_field()
+
+    def stats(self):
+        return self.p.stats()
+
+    def close(self):
+        self.p.close()
+
+
+def solve_sharded_local(kind, cmap, goal, parts, level=None, device=0, occ=1.0, start=(0.0, 0.0)):
+    """Plan `cmap` as `parts` row bands on ONE GPU and return the assembled field (the test of the band path)."""
+    cls = _planner.PLANNERS[kind]
+    level = cls.max_level if level is None else level
+    L, W = cmap.shape
+    bands = [GpuBand(kind, level, L, W, parts, r, device) for r in range(parts)]
+    for b in bands:
+        b.set_map_from_global(cmap, occ)
+        b.set_endpoints(start, goal)
+    outer = run_bands_local(bands)
+    field = np.concatenate([b.read_owned() for b in bands], axis=0)
+    stats = [b.stats() for b in bands]
+    for b in bands:
+        b.close()
+    return field, outer, stats
+
+
+# ---- bench.py --workload bands -------------------------------------------------------------------------------
+def bench_main(args, rank, world):
+    """FD* initial plan of ONE side x side synthetic grid cut into `world` row bands, one per GPU (cfg4 shape;
+    the side defaults to 16384 so the default run stays within minutes — pass --side 65536 for the named size).
+    value = side^2 / time to global convergence (max over ranks), scaling "strong"."""
+    import json
+    import os
+    import time
+
+    import torch
+    import torch.distributed as dist
+    from . import synth
+
+    local = int(os.environ.get("LOCAL_RANK", rank))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    side = args.side if args.side != 4096 else 16384
+    kind = _planner.FD
+    start, goal = synth.default_endpoints(side, side)
+    band = GpuBand(kind, 1, side, side, world, rank, device=local)
+    band.synth_map(3, 10, start, goal)
+    band.set_endpoints(start, goal)
+    comm = DistComm(dist, rank, world, device=torch.device("cuda", local))
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    outer = 0
+    for _ in range(args.warmup):
+        outer = run_bands(band, comm)
+    barrier()
+    t0 = time.perf_counter()
+    kernel_ms = 0.0
+    visits = 0
+    for _ in range(args.steps):
+        outer = run_bands(band, comm)
+        st = band.stats()
+        kernel_ms += st["kernel_ms_solve"]
+        visits += st["tile_visits"]
+    barrier()
+    dt = time.perf_counter() - t0
+    tm = torch.tensor([dt, kernel_ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+    if rank == 0:
+        ms = float(tm[0]) / args.steps * 1e3
+        cells = side * side
+        print(json.dumps({
+            "metric": "Mcells/s to convergence (initial plan), FD* %dx%d in row bands" % (side, side),
+            "value": cells / (ms / 1e3) / 1e6, "unit": "Mcells/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "bands (cfg4 shape)", "planner": "FD* level 1", "grid": "%dx%d" % (side, side),
+                       "bands": world, "halo_exchanges_per_plan": outer, "collective": "NCCL send/recv of one "
+                       "boundary row per neighbour + all-reduce of lowered-halo counts per outer iteration",
+                       "timing": "wall clock between barriers (host-driven outer loop), max over ranks"},
+            "work": {"solver_kernel_ms_max_rank": float(tm[1]) / args.steps,
+                     "tile_visits_per_tile_rank0": visits / args.steps / max(band.stats()["tiles"], 1)}}), flush=True)
+    band.close()
+    if world > 1:
+        dist.destroy_process_group()

@@ -29,7 +29,7 @@ constexpr int TS = 32;         // tile side (elements)
 constexpr int GP = 35;         // shared-memory pitch of the value tile (34 used; odd => row and column
                                // sweeps are both bank-conflict free)
 constexpr int CP = 35;         // shared-memory pitch of the cost tile (33 used for node planners)
-constexpr int NTHREADS = 128;  // 4 warps = 4 sweep directions
+constexpr int NTHREADS = 256;  // one thread per 1x4 strip of the tile
 constexpr int ST_DIRTY = 1;
 constexpr int ST_RUN = 2;
 constexpr int ST_FAR = 4;      // queued, but parked in the far pile (key >= current threshold)
@@ -185,7 +185,9 @@ __device__ inline void advance_threshold(const GridDesc &d, int *s_red, int tid)
     m = __reduce_min_sync(0xffffffffu, m);
     if ((tid & 31) == 0) s_red[tid >> 5] = m;
     __syncthreads();
-    m = min(min(s_red[0], s_red[1]), min(s_red[2], s_red[3]));
+    m = s_red[0];
+#pragma unroll
+    for (int w = 1; w < NTHREADS / 32; ++w) m = min(m, s_red[w]);
     int nthr = INF_BITS;
     if (m != INF_BITS) {
         const float t = __int_as_float(m) + d.delta;
@@ -219,114 +221,104 @@ __device__ inline void advance_threshold(const GridDesc &d, int *s_red, int tid)
     if (tid == 0) c->far_count[cur] = 0;
 }
 
-// ---- in-tile relaxation: cell-level active list -------------------------------------------------------------------
-// A staged tile keeps one dirty bit per element ("a neighbour changed since this element was last evaluated").
-// Warp w owns rows w, w+4, ..., w+28: every iteration it swaps its rows' dirty words out, compacts the set
-// bits into a list with a ballot-free popc/shuffle scan, evaluates 32 listed elements per instruction, and
-// an element that changed sets the dirty bits of its 8 neighbours (possibly in rows of other warps). The
-// tile is converged when an iteration finds no dirty bit in any warp (__syncthreads_or). Work is proportional
-// to the number of element updates, not to the tile area, so a revisit that only moves a thin strip is cheap.
+// ---- in-tile relaxation: strips with a register copy of their neighbourhood ------------------------------------------
+// Thread t owns the 1x4 strip (row t>>3, columns 4*(t&7)..+3) of the staged tile and keeps, in registers, the 3x6
+// window of values around it as it last saw them. A round = reload the window from shared memory; if any of the
+// 18 values differs from the copy (some neighbour, or the strip itself, changed since this thread last looked)
+// re-evaluate the 4 elements and store the ones that improved; __syncthreads_or of "somebody stored" ends the
+// visit. There are no dirty bitmaps, lists or shared atomics on this path: "dirty" is the comparison, a round
+// costs one window load (conflict-free: rows of the pitch-35 array are 3 banks apart, strips 4) plus, where
+// something changed, four independent evaluations that overlap in the pipeline. Reads may race with the stores
+// of the same round; whichever value a thread saw is what its copy records, so a missed store shows up as a
+// difference in the next round. The visit ends after a round without stores, when every thread's copy equals the
+// tile and has been evaluated: tile-local fixed point.
 //
 // Direction bits: which halo side of a tile changed (set by the neighbour that wrote it); they select the
-// elements that are dirty when the tile is staged.
+// strips that evaluate in the first round (the others only take their copy).
 constexpr int IN_N = 1, IN_S = 2, IN_W = 4, IN_E = 8, IN_NW = 16, IN_NE = 32, IN_SW = 64, IN_SE = 128, IN_ALL = 256;
+constexpr int SW = 4;             // strip width
+constexpr int WIN_R = 3, WIN_C = SW + 2;
 
-// value an element takes from its staged neighbours; sgp points at the element inside the staged tile
 template <int KIND>
-__device__ __forceinline__ float eval_elem(const volatile float *p, const float *sc, int r, int c) {
+__device__ __forceinline__ float eval_strip_elem(const float (&w)[WIN_R][WIN_C], const float (&cw)[2][SW + 1], int j) {
     Nbr8 nb;
-    nb.n = p[-GP]; nb.s = p[GP]; nb.w = p[-1]; nb.e = p[1];
-    nb.nw = p[-GP - 1]; nb.ne = p[-GP + 1]; nb.sw = p[GP - 1]; nb.se = p[GP + 1];
-    if (KIND == TASI_KIND_DFM) {
-        return dfm_cell(nb, sc[r * CP + c]);
-    } else {
-        const float *q = sc + r * CP + c;  // sc[i][j] = cost of cell (x0-1+i, y0-1+j)
-        const float tl = q[0], tr = q[1], bl = q[CP], br = q[CP + 1];
-        return (KIND == TASI_KIND_FD) ? fd_node(nb, tl, tr, bl, br) : mfd_node(nb, tl, tr, bl, br);
-    }
+    nb.n = w[0][j + 1]; nb.s = w[2][j + 1]; nb.w = w[1][j]; nb.e = w[1][j + 2];
+    nb.nw = w[0][j]; nb.ne = w[0][j + 2]; nb.sw = w[2][j]; nb.se = w[2][j + 2];
+    if (KIND == TASI_KIND_DFM) return dfm_cell(nb, cw[0][j]);
+    // cw[a][b] = cost of cell (row-1+a, col0-1+b): the four cells around node (row, col0+j)
+    const float tl = cw[0][j], tr = cw[0][j + 1], bl = cw[1][j], br = cw[1][j + 1];
+    return (KIND == TASI_KIND_FD) ? fd_node(nb, tl, tr, bl, br) : mfd_node(nb, tl, tr, bl, br);
 }
 
-// mark the 8 neighbours of (r,c) dirty (those inside the owned part of the tile)
-__device__ __forceinline__ void mark_neighbours(unsigned *dirty, int r, int c, int rlim, unsigned colmask) {
-    const unsigned three = (unsigned) ((7ull << c) >> 1);  // bits c-1, c, c+1 clipped to the 32 columns
-    const unsigned m3 = three & colmask;
-    const unsigned m2 = m3 & ~(1u << c);
-    if (r > 0 && m3) atomicOr(&dirty[r - 1], m3);
-    if (m2) atomicOr(&dirty[r], m2);
-    if (r + 1 < rlim && m3) atomicOr(&dirty[r + 1], m3);
-}
-
-// dirty bits of a freshly staged tile from the direction mask
-__device__ __forceinline__ unsigned initial_dirty(int inmask, int r, int rlim, unsigned colmask) {
-    if (r >= rlim) return 0u;
-    unsigned w = 0;
-    if (inmask & IN_ALL) w = 0xffffffffu;
-    if ((inmask & IN_N) && r == 0) w = 0xffffffffu;
-    if ((inmask & IN_S) && r == TS - 1) w = 0xffffffffu;
-    if (inmask & IN_W) w |= 1u;
-    if (inmask & IN_E) w |= 0x80000000u;
-    if ((inmask & IN_NW) && r == 0) w |= 1u;
-    if ((inmask & IN_NE) && r == 0) w |= 0x80000000u;
-    if ((inmask & IN_SW) && r == TS - 1) w |= 1u;
-    if ((inmask & IN_SE) && r == TS - 1) w |= 0x80000000u;
-    return w & colmask;
-}
-
-// Relax (MODE 0) or invalidate (MODE 1) the staged tile to local convergence. Returns this thread's count of
-// changed elements; *evals gets the number of element evaluations. chg[] accumulates which elements changed.
+// Relax (MODE 0) or invalidate (MODE 1) the staged tile to local convergence. w[1][1..4] holds the strip's final
+// values on return; chg gets one bit per strip element that changed during the visit.
 template <int KIND, int MODE>
-__device__ __forceinline__ int relax_tile(float *sg, const float *sc, unsigned *dirty, unsigned *chg,
-                                          unsigned short *wlist, int warp, int lane, int rlim, int clim, int pin_r,
-                                          int pin_c, float tol, unsigned &iters, unsigned &evals) {
+__device__ __forceinline__ int relax_tile(float *sg, const float *sc, int inmask, int row, int col0, int rlim, int clim,
+                                          int pin_r, int pin_c, float tol, float (&w)[WIN_R][WIN_C], unsigned &chg,
+                                          unsigned &iters, unsigned &evals) {
     const float INF = __int_as_float(0x7f800000);
-    const unsigned colmask = clim >= 32 ? 0xffffffffu : ((1u << clim) - 1u);
-    const int row = warp + 4 * (lane >> 2);  // the row whose dirty word this lane helps to unpack
-    const int q = lane & 3;                  // which byte of the word
-    int cnt_changed = 0;
-    for (;;) {
-        unsigned word = 0;
-        if (q == 0) word = atomicExch(&dirty[row], 0u);
-        word = __shfl_sync(0xffffffffu, word, lane & ~3);
-        unsigned slice = (word >> (8 * q)) & 0xffu;
-        const int cnt = __popc(slice);
-        int incl = cnt;
+    // which strip elements exist and may be written (the goal element is pinned, FieldDPlanner_impl.h:47,146)
+    unsigned live = 0;
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const int t = __shfl_up_sync(0xffffffffu, incl, o);
-            if (lane >= o) incl += t;
-        }
-        const int total = __shfl_sync(0xffffffffu, incl, 31);
-        int pos = incl - cnt;
-        while (slice) {
-            const int b = __ffs(slice) - 1;
-            slice &= slice - 1;
-            wlist[pos++] = (unsigned short) ((row << 5) | (8 * q + b));
-        }
-        __syncwarp();
-        for (int i = lane; i < total; i += 32) {
-            const int rc = wlist[i];
-            const int r = rc >> 5, c = rc & 31;
-            volatile float *p = sg + (r + 1) * GP + (c + 1);
-            const float cur = *p;
-            const float v = eval_elem<KIND>(p, sc, r, c);
-            bool changed;
-            if (MODE == 0) {
-                changed = v < cur;
-                if (changed) *p = v;
-            } else {
-                changed = cur < INF && !(r == pin_r && c == pin_c) && v > cur + cur * tol;
-                if (changed) *p = INF;
+    for (int j = 0; j < SW; ++j)
+        if (row < rlim && col0 + j < clim && !(row == pin_r && col0 + j == pin_c)) live |= 1u << j;
+    // costs the strip reads, once per visit
+    float cw[2][SW + 1];
+    if (KIND == TASI_KIND_DFM) {
+#pragma unroll
+        for (int j = 0; j < SW; ++j) cw[0][j] = sc[row * CP + col0 + j];
+    } else {
+#pragma unroll
+        for (int a = 0; a < 2; ++a)
+#pragma unroll
+            for (int b = 0; b < SW + 1; ++b) cw[a][b] = sc[(row + a) * CP + col0 + b];
+    }
+    // first round: strips that touch a changed halo side
+    bool dirty = (inmask & IN_ALL) != 0;
+    dirty |= (inmask & (IN_N | IN_NW | IN_NE)) && row == 0;
+    dirty |= (inmask & (IN_S | IN_SW | IN_SE)) && row == TS - 1;
+    dirty |= (inmask & (IN_W | IN_NW | IN_SW)) && col0 == 0;
+    dirty |= (inmask & (IN_E | IN_NE | IN_SE)) && col0 == TS - SW;
+    const float *base = sg + row * GP + col0;  // window origin: element (row-1, col0-1)
+    int cnt_changed = 0;
+    chg = 0;
+    bool firstround = true;
+    for (;;) {
+        bool diff = false;
+#pragma unroll
+        for (int a = 0; a < WIN_R; ++a)
+#pragma unroll
+            for (int b = 0; b < WIN_C; ++b) {
+                const float x = *(const volatile float *) (base + a * GP + b);
+                diff |= __float_as_int(x) != __float_as_int(w[a][b]);
+                w[a][b] = x;
             }
-            if (changed) {
-                ++cnt_changed;
-                __threadfence_block();  // the value must be visible before the neighbours' dirty bits
-                mark_neighbours(dirty, r, c, rlim, colmask);
-                atomicOr(&chg[r], 1u << c);
+        if (!firstround) dirty = diff;
+        firstround = false;
+        bool stored = false;
+        if (dirty && live) {
+            float v[SW];
+#pragma unroll
+            for (int j = 0; j < SW; ++j) v[j] = eval_strip_elem<KIND>(w, cw, j);
+#pragma unroll
+            for (int j = 0; j < SW; ++j) {
+                const float cur = w[1][j + 1];
+                bool c;
+                if (MODE == 0) c = v[j] < cur;
+                else c = cur < INF && v[j] > cur + cur * tol;
+                c = c && ((live >> j) & 1u);
+                if (c) {
+                    const float nv = (MODE == 0) ? v[j] : INF;
+                    sg[(row + 1) * GP + col0 + 1 + j] = nv;
+                    chg |= 1u << j;
+                    ++cnt_changed;
+                    stored = true;
+                }
             }
+            evals += SW;
         }
-        evals += total;
         ++iters;
-        if (!__syncthreads_or(total > 0)) break;
+        if (!__syncthreads_or(stored)) break;
     }
     return cnt_changed;
 }
@@ -343,17 +335,16 @@ constexpr int C_ROWS_NODE = TS + 1, C_ROWS_CELL = TS;
 constexpr int C_ITERS = (C_ROWS_NODE * GV_PER_ROW + NTHREADS - 1) / NTHREADS;  // 3
 
 template <int KIND, int MODE>
-__global__ void __launch_bounds__(NTHREADS, 8) solver_kernel(GridDesc d) {
+__global__ void __launch_bounds__(NTHREADS, 3) solver_kernel(GridDesc d) {
     __shared__ float sg[(TS + 2) * GP];   // values, rows/cols -1..32
     __shared__ float sc[(TS + 1) * CP];   // cell costs as float, INF = obstacle
-    __shared__ unsigned s_dirty[TS], s_chg[TS];
-    __shared__ unsigned short s_list[NTHREADS / 32][TS * TS / (NTHREADS / 32)];
     __shared__ int s_tile, s_inmask, s_again, s_adv;
     __shared__ int s_kmin[8];             // per neighbour direction: lowest changed value it will read (bits)
     __shared__ int s_red[NTHREADS / 32];
 
     const float INF = __int_as_float(0x7f800000);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int row = tid >> 3, col0 = (tid & 7) * SW;  // this thread's strip
     unsigned long long n_visits = 0, n_iters = 0, n_changed = 0, n_evals = 0;
     long long c_pop = 0, c_stage = 0, c_relax = 0, c_post = 0, c0 = clock64(), c1;
 
@@ -435,44 +426,55 @@ __global__ void __launch_bounds__(NTHREADS, 8) solver_kernel(GridDesc d) {
                     }
                 }
             }
-            if (tid < TS) {
-                s_dirty[tid] = initial_dirty(s_inmask, tid, rlim, colmask);
-                s_chg[tid] = 0u;
-            }
             __syncthreads();
             ++n_visits;
             c1 = clock64(); c_stage += c1 - c0; c0 = c1;
 
-            unsigned it = 0, ev = 0;
-            n_changed += relax_tile<KIND, MODE>(sg, sc, s_dirty, s_chg, s_list[warp], warp, lane, rlim, clim, pin_r,
-                                                pin_c, d.inval_tol, it, ev);
-            n_iters += it;
+            unsigned it = 0, ev = 0, chg = 0;
+            float w[WIN_R][WIN_C];
+#pragma unroll
+            for (int a2 = 0; a2 < WIN_R; ++a2)
+#pragma unroll
+                for (int b2 = 0; b2 < WIN_C; ++b2) w[a2][b2] = 0.0f;
+            n_changed += relax_tile<KIND, MODE>(sg, sc, s_inmask, row, col0, rlim, clim, pin_r, pin_c, d.inval_tol, w, chg,
+                                                it, ev);
+            n_iters += it;   // counted once per CTA below (every thread sees the same number of rounds)
             n_evals += ev;
             c1 = clock64(); c_relax += c1 - c0; c0 = c1;
 
-            // write back what changed; per neighbour direction keep the lowest changed value it reads
-            {
-                const int r = tid >> 2, qq = tid & 3;
-                unsigned slice = (s_chg[r] >> (8 * qq)) & 0xffu;
-                while (slice) {
-                    const int c = 8 * qq + __ffs(slice) - 1;
-                    slice &= slice - 1;
-                    const float v = sg[(r + 1) * GP + (c + 1)];
-                    d.g[(int64_t) (x0 + r) * d.gpitch + (y0 + c)] = v;
-                    const int kb = (MODE == 0) ? __float_as_int(v) : 0;
-                    if (r == 0) {
-                        atomicMin(&s_kmin[0], kb);
-                        if (c == 0) atomicMin(&s_kmin[4], kb);
-                        if (c == TS - 1) atomicMin(&s_kmin[5], kb);
-                    }
-                    if (r == TS - 1) {
-                        atomicMin(&s_kmin[1], kb);
-                        if (c == 0) atomicMin(&s_kmin[6], kb);
-                        if (c == TS - 1) atomicMin(&s_kmin[7], kb);
-                    }
-                    if (c == 0) atomicMin(&s_kmin[2], kb);
-                    if (c == TS - 1) atomicMin(&s_kmin[3], kb);
+            // write back the strip elements that changed; per neighbour direction keep the lowest changed value
+            // it reads
+            if (chg) {
+                float *gp = d.g + (int64_t) (x0 + row) * d.gpitch + (y0 + col0);
+                if (chg == 0xfu) {
+                    *(float4 *) gp = make_float4(w[1][1], w[1][2], w[1][3], w[1][4]);
+                } else {
+#pragma unroll
+                    for (int j = 0; j < SW; ++j)
+                        if ((chg >> j) & 1u) gp[j] = w[1][j + 1];
                 }
+                int kb = INF_BITS, kfirst = INF_BITS, klast = INF_BITS;
+#pragma unroll
+                for (int j = 0; j < SW; ++j)
+                    if ((chg >> j) & 1u) {
+                        const int bits = (MODE == 0) ? __float_as_int(w[1][j + 1]) : 0;
+                        kb = min(kb, bits);
+                        if (j == 0) kfirst = bits;
+                        if (j == SW - 1) klast = bits;
+                    }
+                const bool wcol = col0 == 0 && kfirst != INF_BITS, ecol = col0 == TS - SW && klast != INF_BITS;
+                if (row == 0) {
+                    atomicMin(&s_kmin[0], kb);
+                    if (wcol) atomicMin(&s_kmin[4], kfirst);
+                    if (ecol) atomicMin(&s_kmin[5], klast);
+                }
+                if (row == TS - 1) {
+                    atomicMin(&s_kmin[1], kb);
+                    if (wcol) atomicMin(&s_kmin[6], kfirst);
+                    if (ecol) atomicMin(&s_kmin[7], klast);
+                }
+                if (wcol) atomicMin(&s_kmin[2], kfirst);
+                if (ecol) atomicMin(&s_kmin[3], klast);
             }
             __threadfence();
             __syncthreads();
@@ -546,6 +548,7 @@ __global__ void __launch_bounds__(NTHREADS, 8) solver_kernel(GridDesc d) {
         n_changed += __shfl_down_sync(0xffffffffu, n_changed, o);
     }
     if (lane == 0 && n_changed) atomicAdd(MODE == 0 ? &d.ctl->lowered : &d.ctl->invalidated, n_changed);
+    for (int o = 16; o > 0; o >>= 1) n_evals += __shfl_down_sync(0xffffffffu, n_evals, o);
     if (lane == 0 && n_evals) atomicAdd(&d.ctl->evals, n_evals);
     if (tid == 0) {
         atomicAdd(&d.ctl->visits, n_visits);

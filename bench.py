@@ -7,7 +7,8 @@ synthetic traversability grid with 10 % random obstacles of SURVEY.md 8(d) (seed
 (4090,4090), occupancy threshold 1.0). One step = one plan to convergence (reset + step). With N > 1 every
 rank plans its own grid of the same shape — the "independent queries, one slice per GPU" sharding of the
 north star, no data-path collective — so scaling is weak and value = N * cells / max-over-ranks time.
-`--workload bands` runs the row-band sharded single grid instead (FD*, NCCL halo exchange; N >= 2).
+`--workload bands` runs the row-band sharded single grid instead (FD*, NCCL halo exchange; N >= 2);
+`--workload cfg3` the MFD* 16384^2 plan + replan-latency measurement (1 GPU).
 
 Timing: W warm-up steps, then K steps; each step's device time is taken with CUDA events recorded on the
 planner's own stream inside tasi_step (stats.step_ms_device: field fill + seeding + persistent solver), L2 is
@@ -44,7 +45,7 @@ def parse():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="cfg2", choices=["cfg2", "bands"])
+    ap.add_argument("--workload", default="cfg2", choices=["cfg2", "cfg3", "bands"])
     ap.add_argument("--side", type=int, default=N_SIDE, help="grid side (development only; the contract is 4096)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
@@ -328,6 +329,10 @@ def main():
     if args.workload == "bands":
         from unige_tasi_path_planners_b200 import bands
         bands.bench_main(args, rank, world)
+        return
+    if args.workload == "cfg3":
+        from unige_tasi_path_planners_b200 import replan_bench
+        replan_bench.bench_main(args, rank, world)
         return
     run_b200(args, rank, world)
 

@@ -45,9 +45,10 @@ def parse():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="cfg2", choices=["cfg2", "cfg3", "bands"])
+    ap.add_argument("--workload", default="cfg2", choices=["cfg2", "cfg3", "cfg5", "bands"])
     ap.add_argument("--side", type=int, default=N_SIDE, help="grid side (development only; the contract is 4096)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--full", action="store_true", help="cfg5: the full 64 maps x 64 queries instead of a sample")
     return ap.parse_args()
 
 
@@ -329,6 +330,10 @@ def main():
     if args.workload == "bands":
         from unige_tasi_path_planners_b200 import bands
         bands.bench_main(args, rank, world)
+        return
+    if args.workload == "cfg5":
+        from unige_tasi_path_planners_b200 import batch
+        batch.bench_main(args, rank, world)
         return
     if args.workload == "cfg3":
         from unige_tasi_path_planners_b200 import replan_bench

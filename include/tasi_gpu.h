@@ -124,6 +124,12 @@ int tasi_synth_map(tasi_planner *p, uint64_t seed, int width, int length, int64_
 /* Copies the device cost grid back (length*width bytes). */
 int tasi_read_map(tasi_planner *p, uint8_t *host_out);
 
+/* Cap the number of persistent solver CTAs of this planner (0 = as many as fit on the device). A batch of
+ * independent queries (BASELINE.json cfg5) runs several planners side by side, each on its own stream with a
+ * share of the SMs: a 1024^2 plan never has more than a few dozen active tiles, so a full-device launch per
+ * query would leave most CTAs waiting. No reference counterpart (the reference is single-threaded). */
+int tasi_set_solver_blocks(tasi_planner *p, int max_blocks);
+
 int tasi_get_stats(tasi_planner *p, tasi_stats *out);
 const char *tasi_last_error(tasi_planner *p);
 

@@ -172,3 +172,31 @@ def test_device_synth_map_matches_host():
     p.synth_map(77, 300, 130, row0=0, p_obs=10, start=(5, 5), goal=(120, 290))
     host = synth.synth_map(77, 130, 300, 10, (5, 5), (120, 290))
     assert np.array_equal(p.read_map(), host)
+
+
+@pytest.mark.parametrize("kind", KINDS)
+def test_concurrent_planners_with_capped_ctas(oracle, kind):
+    """Independent handles on their own streams, each with a share of the persistent CTAs (the query-batch mode):
+    four host threads planning different maps at once give the oracle's fields."""
+    import threading
+    L = W = 192
+    maps = [synth.synth_map(300 + i, L, W, 10, (5, 5), (150 + i, 160 - i)) for i in range(4)]
+    out = [None] * 4
+
+    def work(i):
+        p = make(kind)
+        p.set_solver_blocks(16)
+        p.set_occupancy_threshold(1.0)
+        for rep in range(3):
+            p.set_map(maps[i])
+            p.set_start(5.0, 5.0)
+            p.set_goal(150.0 + i, 160.0 - i)
+            assert p.step() == 0
+        out[i] = p.read_field()
+        p.close()
+
+    th = [threading.Thread(target=work, args=(i,)) for i in range(4)]
+    [t.start() for t in th]
+    [t.join() for t in th]
+    for i in range(4):
+        compare(kind, out[i], oracle.solve(kind, maps[i], (150.0 + i, 160.0 - i)))

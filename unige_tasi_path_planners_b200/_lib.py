@@ -60,6 +60,7 @@ SIGNATURES = {
     "tasi_synth_map": (C.c_int, [C.c_void_p, C.c_uint64, C.c_int, C.c_int, C.c_int64, C.c_int, C.c_int, C.c_int,
                                  C.c_int, C.c_int]),
     "tasi_read_map": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "tasi_set_solver_blocks": (C.c_int, [C.c_void_p, C.c_int]),
     "tasi_get_stats": (C.c_int, [C.c_void_p, C.POINTER(Stats)]),
     "tasi_last_error": (C.c_char_p, [C.c_void_p]),
     "tasi_band_config": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, C.c_int]),

@@ -61,7 +61,7 @@ struct tasi_planner {
     bool patch_pending = false;
     uint64_t last_seed_count = 0;
 
-    int solver_blocks = 0;
+    int solver_blocks = 0, max_blocks = 0;
     double timeout_s = 60.0;
     tasi_stats stats{};
     std::string err;
@@ -218,7 +218,8 @@ int run_solver(tasi_planner *p, int mode, float *ms) {
     const int nt = p->TX * p->TY;
     enqueue_seeds_kernel<<<std::min((nt + 255) / 256, 1024), 256, 0, p->stream>>>(d);
     arm_solver_kernel<<<1, 1, 0, p->stream>>>(d);
-    pick_solver(p->kind, mode)<<<p->solver_blocks, NTHREADS, 0, p->stream>>>(d);
+    const int nblocks = (p->max_blocks > 0 && p->max_blocks < p->solver_blocks) ? p->max_blocks : p->solver_blocks;
+    pick_solver(p->kind, mode)<<<nblocks, NTHREADS, 0, p->stream>>>(d);
     CU_TRY(p, cudaGetLastError());
     CU_TRY(p, cudaEventRecord(p->ev1, p->stream));
     DevCtl h;
@@ -554,6 +555,12 @@ int tasi_cost_device(tasi_planner *p, uint8_t **dev_ptr, int64_t *pitch_bytes) {
     if (!p || !p->c_base) return TASI_ERR_ARG;
     if (dev_ptr) *dev_ptr = c_origin(p);
     if (pitch_bytes) *pitch_bytes = p->cpitch;
+    return TASI_OK;
+}
+
+int tasi_set_solver_blocks(tasi_planner *p, int max_blocks) {
+    if (!p || max_blocks < 0) return TASI_ERR_ARG;
+    p->max_blocks = max_blocks;
     return TASI_OK;
 }
 

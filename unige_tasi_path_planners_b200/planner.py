@@ -174,6 +174,10 @@ class GpuPlanner:
         self.length, self.width = length, width
         self._check(self._L.tasi_synth_map(self._h, seed, width, length, row0, p_obs, sx, sy, gx, gy))
 
+    def set_solver_blocks(self, max_blocks):
+        """Cap the persistent solver CTAs (0 = whole device): lets several planners run side by side."""
+        self._check(self._L.tasi_set_solver_blocks(self._h, int(max_blocks)))
+
     def stats(self):
         s = _lib.Stats()
         self._check(self._L.tasi_get_stats(self._h, C.byref(s)))

@@ -352,7 +352,7 @@ __global__ void __launch_bounds__(NTHREADS, 3) solver_kernel(GridDesc d) {
     __shared__ int s_red[NTHREADS / 32];
 
     const float INF = __int_as_float(0x7f800000);
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tid = threadIdx.x, lane = tid & 31;
     const int row = tid >> 3, col0 = (tid & 7) * SW;  // this thread's strip
     unsigned long long n_visits = 0, n_iters = 0, n_changed = 0, n_evals = 0;
     long long c_pop = 0, c_stage = 0, c_relax = 0, c_post = 0, c0 = clock64(), c1;
@@ -380,7 +380,6 @@ __global__ void __launch_bounds__(NTHREADS, 3) solver_kernel(GridDesc d) {
         const int tx = tile / d.TY, ty = tile - tx * d.TY;
         const int x0 = tx * TS, y0 = ty * TS;
         const int rlim = min(TS, d.EX - x0), clim = min(TS, d.EY - y0);
-        const unsigned colmask = clim >= 32 ? 0xffffffffu : ((1u << clim) - 1u);
         const int pin_r = d.pin_x - x0, pin_c = d.pin_y - y0;
 
         // cell costs around the tile (immutable while the solver runs): issue the loads now, convert after the

@@ -344,7 +344,7 @@ constexpr int C_ROWS_NODE = TS + 1, C_ROWS_CELL = TS;
 constexpr int C_ITERS = (C_ROWS_NODE * GV_PER_ROW + NTHREADS - 1) / NTHREADS;  // 3
 
 template <int KIND, int MODE>
-__global__ void __launch_bounds__(NTHREADS, 3) solver_kernel(GridDesc d) {
+__global__ void __launch_bounds__(NTHREADS, 2) solver_kernel(GridDesc d) {
     __shared__ float sg[(TS + 2) * GP];   // values, rows/cols -1..32
     __shared__ float sc[(TS + 1) * CP];   // cell costs as float, INF = obstacle
     __shared__ int s_tile, s_inmask, s_again, s_adv, s_cap, s_hold;

@@ -61,6 +61,7 @@ typedef struct tasi_stats {
     /* where the persistent CTAs spent their time in the solve phase (SM cycles summed over CTAs): waiting for a
      * tile, staging it, relaxing it, writing back + activating neighbours */
     uint64_t cyc_pop, cyc_stage, cyc_relax, cyc_post;
+    uint64_t cyc_advance;      /* cycles one CTA spent advancing the threshold while all others waited */
 } tasi_stats;
 
 /* Planner object. kind = TASI_FD|TASI_DFM|TASI_MFD; level = the reference's OPT_LVL template argument

@@ -33,7 +33,7 @@ class Stats(C.Structure):
                 ("solver_blocks", C.c_int32),
                 ("solver_launches", C.c_int32),
                 ("cyc_pop", C.c_uint64), ("cyc_stage", C.c_uint64), ("cyc_relax", C.c_uint64),
-                ("cyc_post", C.c_uint64)]
+                ("cyc_post", C.c_uint64), ("cyc_advance", C.c_uint64)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}

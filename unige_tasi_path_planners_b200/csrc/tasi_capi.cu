@@ -241,6 +241,7 @@ int run_solver(tasi_planner *p, int mode, float *ms) {
         p->stats.elem_evals += h.evals;
         p->stats.cyc_pop += h.cyc_pop; p->stats.cyc_stage += h.cyc_stage;
         p->stats.cyc_relax += h.cyc_relax; p->stats.cyc_post += h.cyc_post;
+        p->stats.cyc_advance += h.cyc_advance;
     } else {
         p->stats.inval_visits += h.visits;
         p->stats.elem_invalidated += h.invalidated;

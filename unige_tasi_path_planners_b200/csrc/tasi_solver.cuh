@@ -52,6 +52,7 @@ struct DevCtl {
     unsigned long long far_parked;  // activations that went to the far pile
     unsigned long long evals;       // element evaluations
     unsigned long long cyc_pop, cyc_stage, cyc_relax, cyc_post;  // SM cycles summed over CTAs (thread 0's clock)
+    unsigned long long cyc_advance;  // cycles the advancing CTA spent raising the threshold (all others wait)
     // patch bookkeeping
     unsigned long long n_changed, n_raised, n_lowered_cells, n_seed_elems;
     unsigned long long halo_lowered;
@@ -241,7 +242,6 @@ constexpr int WIN_R = 3, WIN_C = SW + 2;
 
 template <int KIND>
 __device__ __forceinline__ float eval_strip_elem(const float (&w)[WIN_R][WIN_C], const float (&cw)[2][SW + 1], int j) {
-    // w is the window as the evaluation may see it (values at or above the visit's cap already replaced by INF)
     Nbr8 nb;
     nb.n = w[0][j + 1]; nb.s = w[2][j + 1]; nb.w = w[1][j]; nb.e = w[1][j + 2];
     nb.nw = w[0][j]; nb.ne = w[0][j + 2]; nb.sw = w[2][j]; nb.se = w[2][j + 2];
@@ -255,7 +255,7 @@ __device__ __forceinline__ float eval_strip_elem(const float (&w)[WIN_R][WIN_C],
 // values on return; chg gets one bit per strip element that changed during the visit.
 template <int KIND, int MODE>
 __device__ __forceinline__ int relax_tile(float *sg, const float *sc, int inmask, int row, int col0, int rlim, int clim,
-                                          int pin_r, int pin_c, float tol, float cap, float (&w)[WIN_R][WIN_C],
+                                          int pin_r, int pin_c, float tol, float (&w)[WIN_R][WIN_C],
                                           unsigned &chg, unsigned &iters, unsigned &evals) {
     const float INF = __int_as_float(0x7f800000);
     // which strip elements exist and may be written (the goal element is pinned, FieldDPlanner_impl.h:47,146)
@@ -298,17 +298,9 @@ __device__ __forceinline__ int relax_tile(float *sg, const float *sc, int inmask
         firstround = false;
         bool stored = false;
         if (dirty && live) {
-            // Values at or above the cap (the upper end of the value band being settled) are not propagated in
-            // this visit: they are tentative, and spreading them only makes work that a later, lower wave redoes.
-            // They stay stored; the tile parks itself until the band reaches them (hold, below).
-            float wm[WIN_R][WIN_C];
-#pragma unroll
-            for (int a = 0; a < WIN_R; ++a)
-#pragma unroll
-                for (int b = 0; b < WIN_C; ++b) wm[a][b] = (MODE == 0 && !(w[a][b] < cap)) ? INF : w[a][b];
             float v[SW];
 #pragma unroll
-            for (int j = 0; j < SW; ++j) v[j] = eval_strip_elem<KIND>(wm, cw, j);
+            for (int j = 0; j < SW; ++j) v[j] = eval_strip_elem<KIND>(w, cw, j);
 #pragma unroll
             for (int j = 0; j < SW; ++j) {
                 const float cur = w[1][j + 1];
@@ -347,7 +339,7 @@ template <int KIND, int MODE>
 __global__ void __launch_bounds__(NTHREADS, 2) solver_kernel(GridDesc d) {
     __shared__ float sg[(TS + 2) * GP];   // values, rows/cols -1..32
     __shared__ float sc[(TS + 1) * CP];   // cell costs as float, INF = obstacle
-    __shared__ int s_tile, s_inmask, s_again, s_adv, s_cap, s_hold;
+    __shared__ int s_tile, s_inmask, s_again, s_adv;
     __shared__ int s_kmin[8];             // per neighbour direction: lowest changed value it will read (bits)
     __shared__ int s_red[NTHREADS / 32];
 
@@ -369,8 +361,6 @@ __global__ void __launch_bounds__(NTHREADS, 2) solver_kernel(GridDesc d) {
                 __threadfence();
             }
             s_tile = t;
-            s_cap = cur_thr_bits(d);  // constant while any tile runs: the threshold only advances when all are idle
-            s_hold = INF_BITS;
         }
         if (tid < 8) s_kmin[tid] = INF_BITS;
         __syncthreads();
@@ -446,22 +436,8 @@ __global__ void __launch_bounds__(NTHREADS, 2) solver_kernel(GridDesc d) {
             for (int a2 = 0; a2 < WIN_R; ++a2)
 #pragma unroll
                 for (int b2 = 0; b2 < WIN_C; ++b2) w[a2][b2] = 0.0f;
-            const int capbits = s_cap;
-            n_changed += relax_tile<KIND, MODE>(sg, sc, s_inmask, row, col0, rlim, clim, pin_r, pin_c, d.inval_tol,
-                                                __int_as_float(capbits), w, chg, it, ev);
-            if (MODE == 0 && capbits != INF_BITS) {
-                // lowest value in this strip's window (tile + halo ring) that the cap kept out of this visit
-                int hm = INF_BITS;
-#pragma unroll
-                for (int a2 = 0; a2 < WIN_R; ++a2)
-#pragma unroll
-                    for (int b2 = 0; b2 < WIN_C; ++b2) {
-                        const int bits = __float_as_int(w[a2][b2]);  // values are >= 0: int order == float order
-                        if (bits >= capbits && bits < INF_BITS) hm = min(hm, bits);
-                    }
-                hm = __reduce_min_sync(0xffffffffu, hm);
-                if (lane == 0 && hm != INF_BITS) atomicMin(&s_hold, hm);
-            }
+            n_changed += relax_tile<KIND, MODE>(sg, sc, s_inmask, row, col0, rlim, clim, pin_r, pin_c, d.inval_tol, w, chg,
+                                                it, ev);
             n_iters += it;   // counted once per CTA below (every thread sees the same number of rounds)
             n_evals += ev;
             c1 = clock64(); c_relax += c1 - c0; c0 = c1;
@@ -521,17 +497,7 @@ __global__ void __launch_bounds__(NTHREADS, 2) solver_kernel(GridDesc d) {
                 if (MODE == 1) d.seed[tile] = 1;  // phase 2 revisits every tile phase 1 looked at
                 // leave the tile, unless a neighbour changed our halo meanwhile
                 int again_f = 0;
-                const int hold = s_hold;
-                s_hold = INF_BITS;
-                int old;
-                if (hold != INF_BITS) {
-                    // held values: the tile must come back once the band reaches the lowest of them
-                    atomicMin(&d.key[tile], hold);
-                    __threadfence();
-                    old = atomicOr(&d.state[tile], ST_DIRTY) | ST_DIRTY;
-                } else {
-                    old = atomicCAS(&d.state[tile], ST_RUN, 0);
-                }
+                int old = atomicCAS(&d.state[tile], ST_RUN, 0);
                 if (old != ST_RUN) {  // RUN|DIRTY + direction bits
                     const int kk = atomicMin(&d.key[tile], INF_BITS);  // atomic read
                     if (kk < cur_thr_bits(d) || kk == INF_BITS) {
@@ -542,10 +508,7 @@ __global__ void __launch_bounds__(NTHREADS, 2) solver_kernel(GridDesc d) {
                         __threadfence();
                         again_f = 1;
                     } else {
-                        // RUN|DIRTY -> DIRTY|FAR, direction bits stay; the next visit has another cap, so every
-                        // strip evaluates
-                        atomicOr(&d.state[tile], IN_ALL << ST_SHIFT);
-                        atomicXor(&d.state[tile], ST_RUN | ST_FAR);
+                        atomicXor(&d.state[tile], ST_RUN | ST_FAR);  // RUN|DIRTY -> DIRTY|FAR, direction bits stay
                         far_append(d, tile);
                     }
                 }
@@ -562,6 +525,7 @@ __global__ void __launch_bounds__(NTHREADS, 2) solver_kernel(GridDesc d) {
         __syncthreads();
         while (s_adv) {
             __syncthreads();
+            const long long ca0 = clock64();
             if (tid == 0) atomicAdd(&d.ctl->pending, 1);  // hold the count while tiles are being pushed
             advance_threshold(d, s_red, tid);
             __syncthreads();
@@ -575,6 +539,7 @@ __global__ void __launch_bounds__(NTHREADS, 2) solver_kernel(GridDesc d) {
                 }
                 if (*(volatile int *) &d.ctl->error) more = 0;
                 s_adv = more;
+                atomicAdd(&d.ctl->cyc_advance, (unsigned long long) (clock64() - ca0));
             }
             __syncthreads();
         }

@@ -157,7 +157,7 @@ int alloc_grid(tasi_planner *p, int W, int rows) {
     if (blocks > nt) blocks = nt;
     p->solver_blocks = blocks;
     unsigned q = 1;
-    while (q < (unsigned) std::max(nt, blocks) + 1u) q <<= 1;
+    while (q < 2u * (unsigned) std::max(nt, blocks) + 1u) q <<= 1;
     p->qsize = q;
     CU_TRY(p, cudaMalloc(&p->g_base, sizeof(float) * p->gpitch * p->g_rows));
     CU_TRY(p, cudaMalloc(&p->c_base, (size_t) p->cpitch * p->g_rows));

@@ -80,6 +80,11 @@ struct GridDesc {
     float inval_tol;       // relative slack of the invalidate test (0 for FD*/MFD*)
 };
 
+// Release/acquire fence at device scope. __threadfence() compiles to the sequentially consistent MEMBAR.SC.GPU;
+// the queue protocol only needs "my (and, after a CTA barrier, my CTA's) earlier writes are visible before my next
+// atomic", which the acq_rel fence gives (cumulative over the barrier) at a fraction of the latency.
+__device__ __forceinline__ void fence_gpu() { asm volatile("fence.acq_rel.gpu;" ::: "memory"); }
+
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
     unsigned long long t;
     asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
@@ -95,13 +100,9 @@ __device__ __forceinline__ void q_fail(const GridDesc &d) {
 __device__ inline void q_push(const GridDesc &d, int tile) {
     atomicAdd(&d.ctl->pending, 1);
     unsigned long long t = atomicAdd(&d.ctl->tail, 1ULL);
-    int *slot = &d.queue[(unsigned) t & d.qmask];
-    unsigned long long t0 = 0;
-    while (atomicCAS(slot, 0, tile + 1) != 0) {  // slot still held by a slow popper of the previous lap
-        if (t0 == 0) t0 = globaltimer_ns();
-        else if (globaltimer_ns() - t0 > d.ctl->timeout_ns) { q_fail(d); return; }
-        __nanosleep(64);
-    }
+    // The ring has >= 2 x tiles slots and a tile is queued at most once, so the slot of this ticket was emptied by
+    // its previous owner long ago (CTAs are not preempted individually): publish without waiting for a reply.
+    atomicExch(&d.queue[(unsigned) t & d.qmask], tile + 1);
 }
 
 __device__ inline int q_pop(const GridDesc &d) {
@@ -147,8 +148,7 @@ __device__ inline void far_append(const GridDesc &d, int tile) {
 }
 
 __device__ inline void activate(const GridDesc &d, int tile, int kbits, int dirbit) {
-    atomicMin(&d.key[tile], kbits);
-    __threadfence();  // the key must be in place before the state says "queued"
+    atomicMin(&d.key[tile], kbits);  // may land after the state bit: a stale low key only makes the tile look due
     const bool near = kbits < cur_thr_bits(d);
     // one atomic both flags the tile and records which of its halo sides changed (bits ST_SHIFT..)
     const int old = atomicOr(&d.state[tile], ST_DIRTY | (dirbit << ST_SHIFT));
@@ -358,7 +358,7 @@ __global__ void __launch_bounds__(NTHREADS, 2) solver_kernel(GridDesc d) {
                 const int old = atomicExch(&d.state[t], ST_RUN);
                 s_inmask = old >> ST_SHIFT;
                 atomicExch(&d.key[t], INF_BITS);
-                __threadfence();
+                fence_gpu();
             }
             s_tile = t;
         }
@@ -476,8 +476,8 @@ __global__ void __launch_bounds__(NTHREADS, 2) solver_kernel(GridDesc d) {
                 if (wcol) atomicMin(&s_kmin[2], kfirst);
                 if (ecol) atomicMin(&s_kmin[3], klast);
             }
-            __threadfence();
             __syncthreads();
+            if (tid < 9) fence_gpu();  // the CTA's write-back (ordered by the barrier) before the flags below
 
             // activate the neighbours that read a changed border, one thread per direction
             // (0 N, 1 S, 2 W, 3 E, 4 NW, 5 NE, 6 SW, 7 SE); our north border is the south halo of the tile above
@@ -491,9 +491,8 @@ __global__ void __launch_bounds__(NTHREADS, 2) solver_kernel(GridDesc d) {
                 const int nx = tx + dx, ny = ty + dy;
                 if (k != INF_BITS && nx >= 0 && nx < d.TX && ny >= 0 && ny < d.TY) activate(d, nx * d.TY + ny, k, seen_as);
             }
-            __syncthreads();
-
-            if (tid == 0) {
+            // ... while thread 8 leaves the tile (a neighbour may re-queue it at once: we no longer touch its values)
+            if (tid == 8) {
                 if (MODE == 1) d.seed[tile] = 1;  // phase 2 revisits every tile phase 1 looked at
                 // leave the tile, unless a neighbour changed our halo meanwhile
                 int again_f = 0;
@@ -505,7 +504,7 @@ __global__ void __launch_bounds__(NTHREADS, 2) solver_kernel(GridDesc d) {
                         old = atomicExch(&d.state[tile], ST_RUN);
                         s_inmask = old >> ST_SHIFT;
                         atomicExch(&d.key[tile], INF_BITS);
-                        __threadfence();
+                        fence_gpu();
                         again_f = 1;
                     } else {
                         atomicXor(&d.state[tile], ST_RUN | ST_FAR);  // RUN|DIRTY -> DIRTY|FAR, direction bits stay

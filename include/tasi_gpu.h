@@ -150,6 +150,12 @@ int tasi_band_import(tasi_planner *p, int side, uint64_t *n_lowered);
 int tasi_band_begin(tasi_planner *p);
 /* Drain the local work queue to convergence; n_active_out = tiles processed. */
 int tasi_band_solve(tasi_planner *p, uint64_t *n_tile_visits);
+/* Same, but the value threshold of the tile schedule never passes `limit`: tiles whose lowest pending value is at
+ * or beyond it stay parked (they survive to the next call). next_key = the lowest parked value (+INF: nothing
+ * parked). Lets all bands of a grid work on the same band of values between two halo exchanges. */
+int tasi_band_solve_until(tasi_planner *p, float limit, uint64_t *n_tile_visits, float *next_key);
+/* Width of the value band one threshold advance covers on this band's map (delta_factor * 32 * mean free cost). */
+int tasi_band_delta(tasi_planner *p, float *delta);
 
 #ifdef __cplusplus
 }

@@ -54,6 +54,13 @@ class CpuBand:
             n += 1
         return n
 
+    def solve_until(self, limit):
+        self.solve()  # a band may ignore the limit: it then reports nothing parked
+        return float("inf")
+
+    def delta(self):
+        return 64.0
+
     def send_row(self, side):
         return self.gt[self.a] if side == 0 else self.gt[self.b - 1]
 
@@ -76,7 +83,9 @@ def main():
     goal = (float(L - 4), float(W - 5))
     cmap = synth.synth_map(5, L, W, 12, (2, 2), goal)
     band = CpuBand(kind, cmap, goal, parts, rank)
-    outer = bands.run_bands(band, bands.DistComm(dist, rank, parts))
+    comm = bands.DistComm(dist, rank, parts)
+    outer = bands.run_bands_ordered(band, comm, 2) if len(sys.argv) > 4 and sys.argv[4] == "ordered" else \
+        bands.run_bands(band, comm)
     np.save(out + ".%d.npy" % rank, band.g[band.a:band.b])
     with open(out + ".%d.txt" % rank, "w") as f:
         f.write(str(outer))

@@ -40,12 +40,12 @@ def _free_port():
     return p
 
 
-@pytest.mark.parametrize("kind,parts", [(0, 2), (1, 2), (2, 3)])
-def test_gloo_bands_equal_single_domain(oracle, kind, parts, tmp_path):
+@pytest.mark.parametrize("kind,parts,mode", [(0, 2, "plain"), (1, 2, "plain"), (2, 3, "plain"), (0, 2, "ordered")])
+def test_gloo_bands_equal_single_domain(oracle, kind, parts, mode, tmp_path):
     out = str(tmp_path / "band")
     env = dict(os.environ, MASTER_ADDR="127.0.0.1", MASTER_PORT=str(_free_port()), WORLD_SIZE=str(parts),
                OMP_NUM_THREADS="1")
-    procs = [subprocess.Popen([sys.executable, os.path.join(HERE, "_band_worker.py"), str(kind), str(parts), out],
+    procs = [subprocess.Popen([sys.executable, os.path.join(HERE, "_band_worker.py"), str(kind), str(parts), out, mode],
                               env=dict(env, RANK=str(r)), stdout=subprocess.PIPE, stderr=subprocess.STDOUT)
              for r in range(parts)]
     for p in procs:
@@ -69,8 +69,8 @@ def test_gloo_bands_equal_single_domain(oracle, kind, parts, tmp_path):
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("kind", [0, 1, 2])
-@pytest.mark.parametrize("parts", [2, 3, 5])
-def test_gpu_bands_equal_unsharded(kind, parts):
+@pytest.mark.parametrize("parts,ordered", [(2, 0), (3, 0), (5, 0), (2, 1), (3, 4), (4, 2)])
+def test_gpu_bands_equal_unsharded(kind, parts, ordered):
     from unige_tasi_path_planners_b200 import PLANNERS
     L, W = 230, 190
     start, goal = (5.0, 5.0), (float(L - 60), float(W - 6))
@@ -83,7 +83,7 @@ def test_gpu_bands_equal_unsharded(kind, parts):
     assert p.step() == 0
     want = p.read_field()
     p.close()
-    got, outer, stats = bands.solve_sharded_local(kind, cmap, goal, parts, start=start)
+    got, outer, stats = bands.solve_sharded_local(kind, cmap, goal, parts, start=start, ordered=ordered)
     assert got.shape == want.shape
     assert outer >= 2
     if kind == 1:

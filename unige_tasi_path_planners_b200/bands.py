@@ -73,6 +73,13 @@ class DistComm:
             self.dist.all_reduce(t, op=self.dist.ReduceOp.SUM)
         return int(t.item())
 
+    def reduce_float(self, value, op="min"):
+        import torch
+        t = torch.tensor([float(value)], dtype=torch.float64, device=self.device if self.device is not None else "cpu")
+        if self.world > 1:
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.MIN if op == "min" else self.dist.ReduceOp.MAX)
+        return float(t.item())
+
 
 def run_bands(band, comm, max_outer=1 << 20):
     """Solve to global convergence. Returns the number of outer iterations (halo exchanges)."""
@@ -89,6 +96,64 @@ def run_bands(band, comm, max_outer=1 << 20):
         outer += 1
         if comm.total(lowered) == 0:
             return outer
+        if outer >= max_outer:
+            raise RuntimeError("band solve did not converge in %d exchanges" % max_outer)
+
+
+def run_bands_ordered(band, comm, k_phases=4, max_outer=1 << 20):
+    """As run_bands, but all bands advance through the values together: between two halo exchanges no band's
+    tile schedule passes a common limit (k_phases threshold widths beyond the lowest pending value anywhere), so
+    the bands a wavefront currently spans work at the same time instead of one after the other."""
+    band.begin()
+    step = k_phases * comm.reduce_float(band.delta(), "max")
+    limit = step
+    outer = 0
+    inf = float("inf")
+    while True:
+        parked = band.solve_until(limit)
+        comm.exchange(band)
+        lowered = 0
+        if band.open_top:
+            lowered += band.import_side(0)
+        if band.open_bottom:
+            lowered += band.import_side(1)
+        outer += 1
+        total = comm.total(lowered)
+        gmin = comm.reduce_float(parked, "min")
+        if total == 0 and gmin == inf:
+            return outer
+        if gmin < inf:
+            limit = max(limit, gmin + step)
+        if outer >= max_outer:
+            raise RuntimeError("band solve did not converge in %d exchanges" % max_outer)
+
+
+def run_bands_local_ordered(bands, k_phases=4, max_outer=1 << 20):
+    """run_bands_ordered with all bands in this process."""
+    for b in bands:
+        b.begin()
+    step = k_phases * max(b.delta() for b in bands)
+    limit = step
+    outer = 0
+    inf = float("inf")
+    while True:
+        parked = [b.solve_until(limit) for b in bands]
+        for r in range(len(bands) - 1):
+            bands[r + 1].recv_stage(0).copy_(bands[r].send_row(1))
+            bands[r].recv_stage(1).copy_(bands[r + 1].send_row(0))
+        _sync(bands)
+        lowered = 0
+        for b in bands:
+            if b.open_top:
+                lowered += b.import_side(0)
+            if b.open_bottom:
+                lowered += b.import_side(1)
+        outer += 1
+        gmin = min(parked)
+        if lowered == 0 and gmin == inf:
+            return outer
+        if gmin < inf:
+            limit = max(limit, gmin + step)
         if outer >= max_outer:
             raise RuntimeError("band solve did not converge in %d exchanges" % max_outer)
 
@@ -177,6 +242,12 @@ class GpuBand:
     def solve(self):
         return self.p.band_solve()
 
+    def solve_until(self, limit):
+        return self.p.band_solve_until(limit)
+
+    def delta(self):
+        return self.p.band_delta()
+
     def send_row(self, side):
         return self._rows[side][0]
 
@@ -197,7 +268,7 @@ class GpuBand:
         self.p.close()
 
 
-def solve_sharded_local(kind, cmap, goal, parts, level=None, device=0, occ=1.0, start=(0.0, 0.0)):
+def solve_sharded_local(kind, cmap, goal, parts, level=None, device=0, occ=1.0, start=(0.0, 0.0), ordered=0):
     """Plan `cmap` as `parts` row bands on ONE GPU and return the assembled field (the test of the band path)."""
     cls = _planner.PLANNERS[kind]
     level = cls.max_level if level is None else level
@@ -206,7 +277,7 @@ def solve_sharded_local(kind, cmap, goal, parts, level=None, device=0, occ=1.0, 
     for b in bands:
         b.set_map_from_global(cmap, occ)
         b.set_endpoints(start, goal)
-    outer = run_bands_local(bands)
+    outer = run_bands_local_ordered(bands, ordered) if ordered else run_bands_local(bands)
     field = np.concatenate([b.read_owned() for b in bands], axis=0)
     stats = [b.stats() for b in bands]
     for b in bands:
@@ -245,15 +316,20 @@ def bench_main(args, rank, world):
             dist.barrier()
         torch.cuda.synchronize()
 
+    k_phases = int(os.environ.get("TASI_BAND_PHASES", "4"))  # 0 = converge fully between exchanges
+
+    def solve():
+        return run_bands_ordered(band, comm, k_phases) if k_phases > 0 else run_bands(band, comm)
+
     outer = 0
     for _ in range(args.warmup):
-        outer = run_bands(band, comm)
+        outer = solve()
     barrier()
     t0 = time.perf_counter()
     kernel_ms = 0.0
     visits = 0
     for _ in range(args.steps):
-        outer = run_bands(band, comm)
+        outer = solve()
         st = band.stats()
         kernel_ms += st["kernel_ms_solve"]
         visits += st["tile_visits"]
@@ -271,7 +347,7 @@ def bench_main(args, rank, world):
             "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": "bands (cfg4 shape)", "planner": "FD* level 1", "grid": "%dx%d" % (side, side),
-                       "bands": world, "halo_exchanges_per_plan": outer, "collective": "NCCL send/recv of one "
+                       "bands": world, "halo_exchanges_per_plan": outer, "threshold_widths_per_exchange": k_phases, "collective": "NCCL send/recv of one "
                        "boundary row per neighbour + all-reduce of lowered-halo counts per outer iteration",
                        "timing": "wall clock between barriers (host-driven outer loop), max over ranks"},
             "work": {"solver_kernel_ms_max_rank": float(tm[1]) / args.steps,

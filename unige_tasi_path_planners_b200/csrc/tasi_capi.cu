@@ -62,6 +62,9 @@ struct tasi_planner {
     uint64_t last_seed_count = 0;
 
     int solver_blocks = 0, max_blocks = 0;
+    // band mode: the parked tiles and the threshold survive from one launch to the next
+    bool band_started = false;
+    int sv_far_sel = 0, sv_far_count[2] = {0, 0}, sv_thr_bits = 0, sv_far_min_bits = INF_BITS;
     double timeout_s = 60.0;
     tasi_stats stats{};
     std::string err;
@@ -208,7 +211,7 @@ int ensure_cost_stats(tasi_planner *p) {
 
 // Queue the flagged tiles and run the persistent solver in `mode` until the queue drains.
 // Adds the launch's counters to p->stats; *ms = CUDA-event time of the three launches.
-int run_solver(tasi_planner *p, int mode, float *ms) {
+int run_solver(tasi_planner *p, int mode, float *ms, bool resume = false, float limit = INFINITY) {
     int rcs = ensure_cost_stats(p);
     if (rcs != TASI_OK) return rcs;
     GridDesc d = make_desc(p);
@@ -216,6 +219,14 @@ int run_solver(tasi_planner *p, int mode, float *ms) {
     memset(&z, 0, sizeof z);
     z.timeout_ns = (unsigned long long) (p->timeout_s * 1e9);
     z.thr_bits = (mode == 1 || p->delta_factor <= 0.0f) ? INF_BITS : 0;  // invalidation needs no order
+    memcpy(&z.limit_bits, &limit, sizeof(int));
+    z.far_min_bits = INF_BITS;
+    if (resume) {  // the far pile (device arrays + tile states) is still as the previous launch left it
+        z.far_sel = p->sv_far_sel;
+        z.far_count[0] = p->sv_far_count[0];
+        z.far_count[1] = p->sv_far_count[1];
+        z.thr_bits = p->sv_thr_bits;
+    }
     // reset queue tickets + per-launch counters, keep the patch bookkeeping
     CU_TRY(p, cudaMemcpyAsync(p->ctl, &z, offsetof(DevCtl, n_changed), cudaMemcpyHostToDevice, p->stream));
     CU_TRY(p, cudaEventRecord(p->ev0, p->stream));
@@ -230,6 +241,11 @@ int run_solver(tasi_planner *p, int mode, float *ms) {
     int rc = read_ctl(p, &h);
     if (rc != TASI_OK) return rc;
     CU_TRY(p, cudaEventElapsedTime(ms, p->ev0, p->ev1));
+    p->sv_far_sel = h.far_sel;
+    p->sv_far_count[0] = std::min(h.far_count[0], p->far_cap);
+    p->sv_far_count[1] = std::min(h.far_count[1], p->far_cap);
+    p->sv_thr_bits = h.thr_bits;
+    p->sv_far_min_bits = (p->sv_far_count[h.far_sel] > 0) ? h.far_min_bits : INF_BITS;
     p->stats.solver_launches += 3;
     p->stats.queue_pushes += h.pushes;
     p->stats.phases += (uint64_t) h.phases;
@@ -622,18 +638,34 @@ int tasi_band_begin(tasi_planner *p) {
     if (rc != TASI_OK) return rc;
     CU_TRY(p, cudaStreamSynchronize(p->stream));
     p->new_goal = p->initialize_search = false;
+    p->band_started = false;
     return TASI_OK;
 }
 
-int tasi_band_solve(tasi_planner *p, uint64_t *n_tile_visits) {
+int tasi_band_solve_until(tasi_planner *p, float limit, uint64_t *n_tile_visits, float *next_key) {
     if (!p || !p->g_base) return TASI_ERR_ARG;
     CU_TRY(p, cudaSetDevice(p->device));
     const uint64_t before = p->stats.tile_visits;
     float ms = 0;
-    int rc = run_solver(p, 0, &ms);
+    int rc = run_solver(p, 0, &ms, p->band_started, limit);
     if (rc != TASI_OK) return rc;
+    p->band_started = true;
     p->stats.kernel_ms_solve += ms;
     if (n_tile_visits) *n_tile_visits = p->stats.tile_visits - before;
+    if (next_key) memcpy(next_key, &p->sv_far_min_bits, sizeof(float));
+    return TASI_OK;
+}
+
+int tasi_band_solve(tasi_planner *p, uint64_t *n_tile_visits) {
+    return tasi_band_solve_until(p, INFINITY, n_tile_visits, nullptr);
+}
+
+int tasi_band_delta(tasi_planner *p, float *delta) {
+    if (!p || !p->g_base || !delta) return TASI_ERR_ARG;
+    CU_TRY(p, cudaSetDevice(p->device));
+    int rc = ensure_cost_stats(p);
+    if (rc != TASI_OK) return rc;
+    *delta = p->delta_factor * (float) TS * p->mean_cost;
     return TASI_OK;
 }
 

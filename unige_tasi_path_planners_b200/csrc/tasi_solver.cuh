@@ -49,6 +49,9 @@ struct DevCtl {
     int far_sel;                    // which of the two far lists takes new entries
     int far_count[2];
     int phases;                     // threshold advances
+    int limit_bits;                 // band mode: the threshold never passes this value (float bits; INF = none)
+    int far_min_bits;               // lowest parked key seen by the last advance (INF = nothing parked)
+    int kick;                       // set by arm_solver: nothing queued but tiles are parked, CTA 0 starts by advancing
     unsigned long long far_parked;  // activations that went to the far pile
     unsigned long long evals;       // element evaluations
     unsigned long long cyc_pop, cyc_stage, cyc_relax, cyc_post;  // SM cycles summed over CTAs (thread 0's clock)
@@ -173,7 +176,9 @@ __device__ inline void activate(const GridDesc &d, int tile, int kbits, int dirb
 // The queue has drained and no tile is running: raise the threshold to (lowest parked key + delta) and move
 // the parked tiles below it into the queue. Runs on ONE CTA while all others wait in q_pop, so the pile is
 // not appended to until the first push below. Returns with s_flag = 1 if nothing is left anywhere.
-__device__ inline void advance_threshold(const GridDesc &d, int *s_red, int tid) {
+// Returns true (to every thread) if the lowest parked key is at or beyond the launch's limit: nothing is released,
+// the pile stays as it is and the launch ends (band mode: the host exchanges halos and raises the limit).
+__device__ inline bool advance_threshold(const GridDesc &d, int *s_red, int tid) {
     DevCtl *c = d.ctl;
     const int cur = *(volatile int *) &c->far_sel;
     const int n = min(*(volatile int *) &c->far_count[cur], d.far_cap);
@@ -189,11 +194,15 @@ __device__ inline void advance_threshold(const GridDesc &d, int *s_red, int tid)
     m = s_red[0];
 #pragma unroll
     for (int w = 1; w < NTHREADS / 32; ++w) m = min(m, s_red[w]);
+    const int lim = *(volatile int *) &c->limit_bits;
+    if (tid == 0) c->far_min_bits = m;
+    if (m != INF_BITS && m >= lim) return true;
     int nthr = INF_BITS;
     if (m != INF_BITS) {
         const float t = __int_as_float(m) + d.delta;
         nthr = __float_as_int(t);
         if (nthr <= m) nthr = m + 1;  // delta lost to rounding: still let the lowest tile through
+        if (nthr > lim) nthr = lim;
     }
     if (tid == 0) {
         c->thr_bits = nthr;
@@ -220,6 +229,33 @@ __device__ inline void advance_threshold(const GridDesc &d, int *s_red, int tid)
     }
     __syncthreads();
     if (tid == 0) c->far_count[cur] = 0;
+    return false;
+}
+
+// The count of pending tiles reached 0 in this CTA (s_adv set by thread 0): raise the threshold until tiles run
+// again, or end the launch (nothing parked, or everything parked lies beyond the limit).
+__device__ inline void drain_and_advance(const GridDesc &d, int *s_red, int *s_adv, int tid) {
+    __syncthreads();
+    while (*s_adv) {
+        __syncthreads();
+        const long long ca0 = clock64();
+        if (tid == 0) atomicAdd(&d.ctl->pending, 1);  // hold the count while tiles are being pushed
+        const bool stalled = advance_threshold(d, s_red, tid);
+        __syncthreads();
+        if (tid == 0) {
+            int more = 0;
+            if (atomicSub(&d.ctl->pending, 1) == 1) {
+                // nothing was pushed (or all of it already finished)
+                const int sel = *(volatile int *) &d.ctl->far_sel;
+                if (!stalled && *(volatile int *) &d.ctl->far_count[sel] > 0) more = 1;
+                else { __threadfence(); atomicExch(&d.ctl->done, 1); }
+            }
+            if (*(volatile int *) &d.ctl->error) more = 0;
+            *s_adv = more;
+            atomicAdd(&d.ctl->cyc_advance, (unsigned long long) (clock64() - ca0));
+        }
+        __syncthreads();
+    }
 }
 
 // ---- in-tile relaxation: strips with a register copy of their neighbourhood ------------------------------------------
@@ -348,6 +384,19 @@ __global__ void __launch_bounds__(NTHREADS, 2) solver_kernel(GridDesc d) {
     const int row = tid >> 3, col0 = (tid & 7) * SW;  // this thread's strip
     unsigned long long n_visits = 0, n_iters = 0, n_changed = 0, n_evals = 0;
     long long c_pop = 0, c_stage = 0, c_relax = 0, c_post = 0, c0 = clock64(), c1;
+
+    // resumed band solve with nothing queued: arm_solver left one virtual pending tile for CTA 0 to retire, which
+    // takes the count to 0 and starts the threshold advance
+    if (blockIdx.x == 0) {
+        if (tid == 0) {
+            s_adv = 0;
+            if (*(volatile int *) &d.ctl->kick) {
+                d.ctl->kick = 0;
+                s_adv = (atomicSub(&d.ctl->pending, 1) == 1) ? 1 : 0;
+            }
+        }
+        drain_and_advance(d, s_red, &s_adv, tid);
+    }
 
     for (;;) {
         if (tid == 0) {
@@ -521,27 +570,7 @@ __global__ void __launch_bounds__(NTHREADS, 2) solver_kernel(GridDesc d) {
 
         // the tile is no longer pending; whoever takes the count to 0 advances the threshold
         if (tid == 0) s_adv = (atomicSub(&d.ctl->pending, 1) == 1) ? 1 : 0;
-        __syncthreads();
-        while (s_adv) {
-            __syncthreads();
-            const long long ca0 = clock64();
-            if (tid == 0) atomicAdd(&d.ctl->pending, 1);  // hold the count while tiles are being pushed
-            advance_threshold(d, s_red, tid);
-            __syncthreads();
-            if (tid == 0) {
-                int more = 0;
-                if (atomicSub(&d.ctl->pending, 1) == 1) {
-                    // nothing was pushed (or all of it already finished)
-                    const int sel = *(volatile int *) &d.ctl->far_sel;
-                    if (*(volatile int *) &d.ctl->far_count[sel] > 0) more = 1;
-                    else { __threadfence(); atomicExch(&d.ctl->done, 1); }
-                }
-                if (*(volatile int *) &d.ctl->error) more = 0;
-                s_adv = more;
-                atomicAdd(&d.ctl->cyc_advance, (unsigned long long) (clock64() - ca0));
-            }
-            __syncthreads();
-        }
+        drain_and_advance(d, s_red, &s_adv, tid);
     }
 
     // per-CTA counters -> global statistics
@@ -598,7 +627,14 @@ __global__ void enqueue_seeds_kernel(GridDesc d) {
 
 // Nothing queued => the solver must see done == 1 or its CTAs would wait for work forever.
 __global__ void arm_solver_kernel(GridDesc d) {
-    d.ctl->done = (d.ctl->pending == 0) ? 1 : 0;
+    DevCtl *c = d.ctl;
+    const bool parked = c->far_count[c->far_sel] > 0;
+    c->kick = 0;
+    if (c->pending == 0 && parked) {  // only parked tiles: a virtual pending tile makes CTA 0 advance the threshold
+        c->pending = 1;
+        c->kick = 1;
+    }
+    c->done = (c->pending == 0) ? 1 : 0;
 }
 
 // Graph::update (ProjectToolkit/Graph.cpp:36-51) on the device cost grid: rows x..x+h-1, cols y..y+w-1 take
@@ -669,9 +705,17 @@ __global__ void band_import_kernel(GridDesc d, const float *stage, int hrow, int
             *hp = nv;
             ++cnt;
             const int ty = yy / TS;
+            const int kb = __float_as_int(nv);
+            atomicMin(&d.key[trow * d.TY + ty], kb);  // a parked tile must be released when the band reaches nv
             d.seed[trow * d.TY + ty] = 1;
-            if ((yy & (TS - 1)) == 0 && ty > 0) d.seed[trow * d.TY + ty - 1] = 1;
-            if ((yy & (TS - 1)) == TS - 1 && ty + 1 < d.TY) d.seed[trow * d.TY + ty + 1] = 1;
+            if ((yy & (TS - 1)) == 0 && ty > 0) {
+                atomicMin(&d.key[trow * d.TY + ty - 1], kb);
+                d.seed[trow * d.TY + ty - 1] = 1;
+            }
+            if ((yy & (TS - 1)) == TS - 1 && ty + 1 < d.TY) {
+                atomicMin(&d.key[trow * d.TY + ty + 1], kb);
+                d.seed[trow * d.TY + ty + 1] = 1;
+            }
         }
     }
     if (cnt) atomicAdd(&d.ctl->halo_lowered, cnt);

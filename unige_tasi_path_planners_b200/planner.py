@@ -210,6 +210,17 @@ class GpuPlanner:
         self._check(self._L.tasi_band_solve(self._h, C.byref(n)))
         return n.value
 
+    def band_solve_until(self, limit):
+        """Solve without letting the schedule's threshold pass `limit`; returns the lowest parked value (inf: none)."""
+        n, k = C.c_uint64(0), C.c_float(0)
+        self._check(self._L.tasi_band_solve_until(self._h, limit, C.byref(n), C.byref(k)))
+        return k.value
+
+    def band_delta(self):
+        d = C.c_float(0)
+        self._check(self._L.tasi_band_delta(self._h, C.byref(d)))
+        return d.value
+
 
 class FieldDPlanner(GpuPlanner):
     """FD* — FieldDPlanner<OPT_LVL> (FieldDStar/FieldDPlanner.h); values on nodes."""

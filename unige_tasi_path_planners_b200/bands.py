@@ -73,6 +73,16 @@ class DistComm:
             self.dist.all_reduce(t, op=self.dist.ReduceOp.SUM)
         return int(t.item())
 
+    def lowered_and_min(self, lowered, parked):
+        """One all-reduce for both convergence quantities: (any halo value lowered anywhere, lowest parked value)."""
+        import torch
+        t = torch.tensor([1.0 if lowered else 0.0, -float(parked)], dtype=torch.float64,
+                         device=self.device if self.device is not None else "cpu")
+        if self.world > 1:
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        v = t.tolist()
+        return v[0] > 0.0, -v[1]
+
     def reduce_float(self, value, op="min"):
         import torch
         t = torch.tensor([float(value)], dtype=torch.float64, device=self.device if self.device is not None else "cpu")
@@ -118,9 +128,8 @@ def run_bands_ordered(band, comm, k_phases=4, max_outer=1 << 20):
         if band.open_bottom:
             lowered += band.import_side(1)
         outer += 1
-        total = comm.total(lowered)
-        gmin = comm.reduce_float(parked, "min")
-        if total == 0 and gmin == inf:
+        any_lowered, gmin = comm.lowered_and_min(lowered, parked)
+        if not any_lowered and gmin == inf:
             return outer
         if gmin < inf:
             limit = max(limit, gmin + step)

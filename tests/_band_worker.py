@@ -82,8 +82,18 @@ def main():
     L, W = 22, 17
     goal = (float(L - 4), float(W - 5))
     cmap = synth.synth_map(5, L, W, 12, (2, 2), goal)
-    band = CpuBand(kind, cmap, goal, parts, rank)
     comm = bands.DistComm(dist, rank, parts)
+    if len(sys.argv) > 4 and sys.argv[4].startswith("cyclic"):
+        per = int(sys.argv[4][6:])
+        bs = bands.BandSet(rank, parts, per, lambda g, n: CpuBand(kind, cmap, goal, n, g))
+        outer = bands.run_bandset_ordered(bs, comm, 2)
+        for g, b in bs.bands.items():
+            np.save(out + ".g%d.npy" % g, b.g[b.a:b.b])
+        with open(out + ".%d.txt" % rank, "w") as f:
+            f.write(str(outer))
+        dist.destroy_process_group()
+        return
+    band = CpuBand(kind, cmap, goal, parts, rank)
     outer = bands.run_bands_ordered(band, comm, 2) if len(sys.argv) > 4 and sys.argv[4] == "ordered" else \
         bands.run_bands(band, comm)
     np.save(out + ".%d.npy" % rank, band.g[band.a:band.b])

@@ -67,6 +67,27 @@ def test_gloo_bands_equal_single_domain(oracle, kind, parts, mode, tmp_path):
     assert len(set(outers)) == 1 and outers[0] >= 2  # every rank left the loop in the same iteration
 
 
+@pytest.mark.parametrize("kind,world,per", [(0, 2, 2), (2, 3, 2), (0, 2, 3)])
+def test_gloo_cyclic_bandset_equal_single_domain(oracle, kind, world, per, tmp_path):
+    """Several cyclically dealt bands per rank: the edge-ordered exchange matches messages between rank pairs."""
+    out = str(tmp_path / "band")
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1", MASTER_PORT=str(_free_port()), WORLD_SIZE=str(world),
+               OMP_NUM_THREADS="1")
+    procs = [subprocess.Popen([sys.executable, os.path.join(HERE, "_band_worker.py"), str(kind), str(world), out,
+                               "cyclic%d" % per], env=dict(env, RANK=str(r)), stdout=subprocess.PIPE,
+                              stderr=subprocess.STDOUT) for r in range(world)]
+    for p in procs:
+        o, _ = p.communicate(timeout=300)
+        assert p.returncode == 0, o.decode()[-3000:]
+    got = np.concatenate([np.load(out + ".g%d.npy" % g) for g in range(world * per)], axis=0)
+    L, W = 22, 17
+    goal = (float(L - 4), float(W - 5))
+    cmap = synth.synth_map(5, L, W, 12, (2, 2), goal)
+    want = oracle.solve(kind, cmap, goal, method="sweep")
+    assert got.shape == want.shape
+    assert np.array_equal(got, want)
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("kind", [0, 1, 2])
 @pytest.mark.parametrize("parts,ordered", [(2, 0), (3, 0), (5, 0), (2, 1), (3, 4), (4, 2)])

@@ -137,6 +137,93 @@ def run_bands_ordered(band, comm, k_phases=4, max_outer=1 << 20):
             raise RuntimeError("band solve did not converge in %d exchanges" % max_outer)
 
 
+class BandSet:
+    """The bands one rank owns under a CYCLIC distribution: with `world` ranks and `per_rank` bands each, rank r
+    owns the global bands r, r + world, r + 2*world, ... of world*per_rank. A wavefront from a corner goal covers
+    only some rows at a time; dealing the bands out cyclically gives every GPU a piece of the front for most of
+    the sweep instead of one contiguous block that is busy a fraction of it.
+
+    `make_band(g, parts)` builds the band object of global index g (GpuBand, or a CPU stand-in in the tests)."""
+
+    def __init__(self, rank, world, per_rank, make_band):
+        self.rank, self.world, self.parts = rank, world, world * per_rank
+        self.ids = [rank + world * j for j in range(per_rank)]
+        self.bands = {g: make_band(g, self.parts) for g in self.ids}
+
+    def owner(self, g):
+        return g % self.world
+
+    def begin(self):
+        for b in self.bands.values():
+            b.begin()
+
+    def delta(self):
+        return max(b.delta() for b in self.bands.values())
+
+    def solve_until(self, limit):
+        return min(b.solve_until(limit) for b in self.bands.values())
+
+    def import_all(self):
+        lowered = 0
+        for b in self.bands.values():
+            if b.open_top:
+                lowered += b.import_side(0)
+            if b.open_bottom:
+                lowered += b.import_side(1)
+        return lowered
+
+    def exchange(self, comm):
+        """Swap boundary rows over every edge (g, g+1) this rank takes part in. Edges are walked in the same global
+        order on every rank, so the messages between any two ranks are posted in matching order (NCCL has no tags)."""
+        ops, local = [], []
+        for g in range(self.parts - 1):
+            up, dn = g in self.bands, (g + 1) in self.bands
+            if up and dn:  # both ends here (world == 1)
+                local.append(g)
+            elif up:       # we own the upper band: its last row goes down, the lower band's first row comes up
+                peer = self.owner(g + 1)
+                ops.append(comm.dist.P2POp(comm.dist.isend, self.bands[g].send_row(1), peer))
+                ops.append(comm.dist.P2POp(comm.dist.irecv, self.bands[g].recv_stage(1), peer))
+            elif dn:
+                peer = self.owner(g)
+                ops.append(comm.dist.P2POp(comm.dist.irecv, self.bands[g + 1].recv_stage(0), peer))
+                ops.append(comm.dist.P2POp(comm.dist.isend, self.bands[g + 1].send_row(0), peer))
+        for g in local:
+            self.bands[g + 1].recv_stage(0).copy_(self.bands[g].send_row(1))
+            self.bands[g].recv_stage(1).copy_(self.bands[g + 1].send_row(0))
+        if ops:
+            for w in comm.dist.batch_isend_irecv(ops):
+                w.wait()
+        if comm.device is not None:
+            import torch
+            torch.cuda.current_stream(comm.device).synchronize()
+
+    def close(self):
+        for b in self.bands.values():
+            b.close()
+
+
+def run_bandset_ordered(bs, comm, k_phases=2, max_outer=1 << 20):
+    """run_bands_ordered for a rank that owns several (cyclically dealt) bands."""
+    bs.begin()
+    step = k_phases * comm.reduce_float(bs.delta(), "max")
+    limit = step
+    outer = 0
+    inf = float("inf")
+    while True:
+        parked = bs.solve_until(limit)
+        bs.exchange(comm)
+        lowered = bs.import_all()
+        outer += 1
+        any_lowered, gmin = comm.lowered_and_min(lowered, parked)
+        if not any_lowered and gmin == inf:
+            return outer
+        if gmin < inf:
+            limit = max(limit, gmin + step)
+        if outer >= max_outer:
+            raise RuntimeError("band solve did not converge in %d exchanges" % max_outer)
+
+
 def run_bands_local_ordered(bands, k_phases=4, max_outer=1 << 20):
     """run_bands_ordered with all bands in this process."""
     for b in bands:
@@ -314,9 +401,16 @@ def bench_main(args, rank, world):
     side = args.side if args.side != 4096 else 16384
     kind = _planner.FD
     start, goal = synth.default_endpoints(side, side)
-    band = GpuBand(kind, 1, side, side, world, rank, device=local)
-    band.synth_map(3, 10, start, goal)
-    band.set_endpoints(start, goal)
+    per_rank = int(os.environ.get("TASI_BANDS_PER_GPU", "4" if world > 1 else "1"))
+
+    def make(g, parts):
+        b = GpuBand(kind, 1, side, side, parts, g, device=local)
+        b.synth_map(3, 10, start, goal)
+        b.set_endpoints(start, goal)
+        return b
+
+    bs = BandSet(rank, world, per_rank, make)
+    band = bs.bands[bs.ids[0]]
     comm = DistComm(dist, rank, world, device=torch.device("cuda", local))
 
     def barrier():
@@ -328,7 +422,10 @@ def bench_main(args, rank, world):
     k_phases = int(os.environ.get("TASI_BAND_PHASES", "4"))  # 0 = converge fully between exchanges
 
     def solve():
-        return run_bands_ordered(band, comm, k_phases) if k_phases > 0 else run_bands(band, comm)
+        if k_phases > 0:
+            return run_bandset_ordered(bs, comm, k_phases)
+        assert per_rank == 1, "the unordered protocol takes one band per rank"
+        return run_bands(band, comm)
 
     outer = 0
     for _ in range(args.warmup):
@@ -339,9 +436,10 @@ def bench_main(args, rank, world):
     visits = 0
     for _ in range(args.steps):
         outer = solve()
-        st = band.stats()
-        kernel_ms += st["kernel_ms_solve"]
-        visits += st["tile_visits"]
+        for b in bs.bands.values():
+            st = b.stats()
+            kernel_ms += st["kernel_ms_solve"]
+            visits += st["tile_visits"]
     barrier()
     dt = time.perf_counter() - t0
     tm = torch.tensor([dt, kernel_ms], dtype=torch.float64, device="cuda")
@@ -356,11 +454,12 @@ def bench_main(args, rank, world):
             "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": "bands (cfg4 shape)", "planner": "FD* level 1", "grid": "%dx%d" % (side, side),
-                       "bands": world, "halo_exchanges_per_plan": outer, "threshold_widths_per_exchange": k_phases, "collective": "NCCL send/recv of one "
+                       "bands": world * per_rank, "bands_per_gpu": per_rank, "distribution": "cyclic", "halo_exchanges_per_plan": outer, "threshold_widths_per_exchange": k_phases, "collective": "NCCL send/recv of one "
                        "boundary row per neighbour + all-reduce of lowered-halo counts per outer iteration",
                        "timing": "wall clock between barriers (host-driven outer loop), max over ranks"},
             "work": {"solver_kernel_ms_max_rank": float(tm[1]) / args.steps,
-                     "tile_visits_per_tile_rank0": visits / args.steps / max(band.stats()["tiles"], 1)}}), flush=True)
-    band.close()
+                     "tile_visits_per_tile_rank0": visits / args.steps / max(sum(b.stats()["tiles"] for b in
+                                                                                   bs.bands.values()), 1)}}), flush=True)
+    bs.close()
     if world > 1:
         dist.destroy_process_group()

@@ -401,7 +401,7 @@ def bench_main(args, rank, world):
     side = args.side if args.side != 4096 else 16384
     kind = _planner.FD
     start, goal = synth.default_endpoints(side, side)
-    per_rank = int(os.environ.get("TASI_BANDS_PER_GPU", "4" if world > 1 else "1"))
+    per_rank = int(os.environ.get("TASI_BANDS_PER_GPU", "1"))
 
     def make(g, parts):
         b = GpuBand(kind, 1, side, side, parts, g, device=local)
@@ -419,7 +419,7 @@ def bench_main(args, rank, world):
             dist.barrier()
         torch.cuda.synchronize()
 
-    k_phases = int(os.environ.get("TASI_BAND_PHASES", "4"))  # 0 = converge fully between exchanges
+    k_phases = int(os.environ.get("TASI_BAND_PHASES", "2"))  # 0 = converge fully between exchanges
 
     def solve():
         if k_phases > 0:

@@ -7,8 +7,8 @@
 //
 //   * the element grid is cut into 32x32 tiles; a persistent grid of CTAs pulls active tiles from a device
 //     ticket queue, stages the tile (+1 halo ring) and the cell costs around it in shared memory, and relaxes it
-//     to tile-local convergence with four concurrent directional Gauss-Seidel sweeps (one warp each:
-//     rows down / rows up / columns right / columns left), accepting only decreases;
+//     to tile-local convergence (relax_tile: one 1x4 strip per thread with a register copy of its neighbourhood),
+//     accepting only decreases;
 //   * a tile whose border changed activates the neighbour tiles that read that border;
 //   * the same machinery run in "invalidate" mode is phase 1 of a replan: an element whose stored value is
 //     no longer supported by its neighbours under the new costs is reset to INF (what the reference's

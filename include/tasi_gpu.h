@@ -98,6 +98,13 @@ int tasi_patch_map(tasi_planner *p, const uint8_t *host_patch, int x, int y, int
 int tasi_set_start(tasi_planner *p, float x, float y);
 int tasi_set_goal(tasi_planner *p, float x, float y);
 
+/* Several goals at once (n pairs x,y): every goal element gets value 0 and the field is the cost to the nearest
+ * goal. No reference counterpart; it is what lets a batch of independent queries run as ONE plan: the maps are
+ * stacked into one tall map with an obstacle row between them (nothing propagates through an obstacle row, and
+ * the node rows either side of it are exactly the boundary rows of the two maps), one goal per map, and all the
+ * wavefronts share one launch of the persistent solver. Always re-plans from scratch. */
+int tasi_set_goals(tasi_planner *p, const float *xy, int n);
+
 /* ReplannerBase::step (ReplannerBase.h:43-75): initial plan, or two-phase repair after patches; returns when
  * the field is converged. Outputs (all optional): u_ms/p_ms = host wall time of the update and plan halves
  * (the reference's u_time/p_time), n_updated/n_expanded = num_nodes_updated/num_nodes_expanded. */

@@ -200,3 +200,33 @@ def test_concurrent_planners_with_capped_ctas(oracle, kind):
     [t.join() for t in th]
     for i in range(4):
         compare(kind, out[i], oracle.solve(kind, maps[i], (150.0 + i, 160.0 - i)))
+
+
+@pytest.mark.parametrize("kind", KINDS)
+def test_stacked_batch_equals_single_plans(oracle, kind):
+    """A batch of independent queries solved as one multi-goal plan on the stacked map (obstacle row between maps):
+    every block is the field a planner holding only that map returns."""
+    from unige_tasi_path_planners_b200 import batch
+    L, W = 70, 100
+    maps = [synth.synth_map(400 + i, L, W, 10, None, None) for i in range(3)]
+    maps.append(maps[1])  # a second query on an already used map
+    goals = [(60.0, 90.0), (5.0, 50.0), (35.0, 3.0), (66.0, 8.0)]
+    for m, g in zip(maps, goals):
+        synth.clear_block(m, int(g[0]), int(g[1]))
+    sb = batch.StackedBatch(kind, device=0)
+    sb.plan(maps, goals)
+    for i, (m, g) in enumerate(zip(maps, goals)):
+        compare(kind, sb.field(i), oracle.solve(kind, m, g))
+    w = sb.window(2, -5, 10, 20, 30)
+    f = sb.field(2)
+    assert np.all(np.isinf(w[:5])) and np.array_equal(w[5:], f[0:15, 10:40])
+    # a replan on the stack: patch map 1's block, every block still equals its own from-scratch plan
+    patch = synth.synth_rows(77, 0, 20, 30, 20)
+    sb.p.patch_map(patch, 1 * (L + 1) + 10, 40)
+    sb.p.set_start(1.0, 1.0)
+    assert sb.p.step() == 0
+    m1 = maps[1].copy()
+    oracle.patch(m1, patch, 10, 40)
+    compare(kind, sb.field(1), oracle.solve(kind, m1, goals[1]))
+    compare(kind, sb.field(0), oracle.solve(kind, maps[0], goals[0]))
+    sb.close()

@@ -51,6 +51,7 @@ SIGNATURES = {
     "tasi_patch_map": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, _u64p]),
     "tasi_set_start": (C.c_int, [C.c_void_p, C.c_float, C.c_float]),
     "tasi_set_goal": (C.c_int, [C.c_void_p, C.c_float, C.c_float]),
+    "tasi_set_goals": (C.c_int, [C.c_void_p, _f32p, C.c_int]),
     "tasi_step": (C.c_int, [C.c_void_p, _f32p, _f32p, _u64p, _u64p]),
     "tasi_field_dims": (C.c_int, [C.c_void_p, _ip, _ip]),
     "tasi_read_window": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),

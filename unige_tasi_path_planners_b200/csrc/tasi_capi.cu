@@ -30,6 +30,9 @@ struct tasi_planner {
     float start_x = 0, start_y = 0, goal_x = 0, goal_y = 0;
     bool have_goal_elem = false;
     int64_t goal_ex = -1, goal_ey = -1;  // goal element, global coordinates
+    std::vector<int2> xgoals;            // further goals (tasi_set_goals), band-local element coordinates
+    int2 *xgoals_dev = nullptr;
+    size_t xgoals_cap = 0;
     uint64_t num_nodes_updated = 0, num_nodes_expanded = 0;
 
     // geometry
@@ -99,6 +102,7 @@ GridDesc make_desc(const tasi_planner *p) {
     int64_t py = p->have_goal_elem ? p->goal_ey : -1;
     if (px < 0 || px >= p->EX || py < 0 || py >= p->EY) { px = -1000000; py = -1000000; }
     d.pin_x = (int) px; d.pin_y = (int) py;
+    d.xgoals = p->xgoals_dev; d.n_xgoals = (int) p->xgoals.size();
     d.state = p->state; d.queue = p->queue; d.qmask = p->qsize - 1;
     d.seed = p->seed; d.ctl = p->ctl;
     d.key = p->key; d.far = p->far; d.far_cap = p->far_cap;
@@ -331,7 +335,7 @@ int tasi_destroy(tasi_planner *p) {
     cudaSetDevice(p->device);
     if (p->stream) cudaStreamSynchronize(p->stream);
     free_grid(p);
-    cudaFree(p->ctl); cudaFree(p->cost_sum); cudaFree(p->patch_buf); cudaFree(p->chg_buf);
+    cudaFree(p->ctl); cudaFree(p->cost_sum); cudaFree(p->patch_buf); cudaFree(p->chg_buf); cudaFree(p->xgoals_dev);
     if (p->ev0) cudaEventDestroy(p->ev0);
     if (p->ev1) cudaEventDestroy(p->ev1);
     if (p->evs0) cudaEventDestroy(p->evs0);
@@ -461,9 +465,38 @@ int tasi_set_goal(tasi_planner *p, float x, float y) {
     int64_t ex, ey;
     round_elem(x, y, &ex, &ey);
     p->new_goal = !p->have_goal_elem || ex != p->goal_ex || ey != p->goal_ey;  // ReplannerBase.h:99-108
+    if (!p->xgoals.empty()) { p->xgoals.clear(); p->new_goal = true; }
     p->goal_x = x; p->goal_y = y; p->goal_ex = ex; p->goal_ey = ey;
     p->have_goal_elem = true;
     p->goal_set = true;
+    return TASI_OK;
+}
+
+int tasi_set_goals(tasi_planner *p, const float *xy, int n) {
+    if (!p || !xy || n < 1) return TASI_ERR_ARG;
+    CU_TRY(p, cudaSetDevice(p->device));
+    int rc = tasi_set_goal(p, xy[0], xy[1]);
+    if (rc != TASI_OK) return rc;
+    p->xgoals.clear();
+    for (int i = 1; i < n; ++i) {
+        int64_t ex, ey;
+        round_elem(xy[2 * i], xy[2 * i + 1], &ex, &ey);
+        ex -= p->global_row0;
+        if (ex < INT32_MIN / 2 || ex > INT32_MAX / 2) continue;
+        p->xgoals.push_back(make_int2((int) ex, (int) ey));
+    }
+    if (p->xgoals.size() > p->xgoals_cap) {
+        cudaFree(p->xgoals_dev);
+        p->xgoals_dev = nullptr; p->xgoals_cap = 0;
+        CU_TRY(p, cudaMalloc(&p->xgoals_dev, sizeof(int2) * p->xgoals.size()));
+        p->xgoals_cap = p->xgoals.size();
+    }
+    if (!p->xgoals.empty()) {
+        CU_TRY(p, cudaMemcpyAsync(p->xgoals_dev, p->xgoals.data(), sizeof(int2) * p->xgoals.size(),
+                                  cudaMemcpyHostToDevice, p->stream));
+        CU_TRY(p, cudaStreamSynchronize(p->stream));
+    }
+    p->new_goal = true;  // a goal set is always planned from scratch
     return TASI_OK;
 }
 

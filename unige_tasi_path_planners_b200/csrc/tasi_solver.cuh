@@ -71,6 +71,8 @@ struct GridDesc {
     int L, W;              // cell rows / columns stored (band-local)
     int thr;               // occupancy threshold byte: cost >= thr is an obstacle (Graph.cpp:262-268)
     int pin_x, pin_y;      // goal element in local coordinates (outside the grid = none)
+    const int2 *xgoals;    // further goal elements (local coordinates) of a multi-goal plan, e.g. a stack of
+    int n_xgoals;          // independent maps solved in one launch (tasi_set_goals)
     int *state;            // TX*TY tile states
     int *queue;            // ring of tile id + 1, 0 = empty
     unsigned qmask;        // ring size - 1
@@ -342,7 +344,7 @@ __device__ __forceinline__ int relax_tile(float *sg, const float *sc, int inmask
                 const float cur = w[1][j + 1];
                 bool c;
                 if (MODE == 0) c = v[j] < cur;
-                else c = cur < INF && v[j] > cur + cur * tol;
+                else c = cur < INF && cur > 0.0f && v[j] > cur + cur * tol;  // 0 = a goal (costs are >= 1): pinned
                 c = c && ((live >> j) & 1u);
                 if (c) {
                     const float nv = (MODE == 0) ? v[j] : INF;
@@ -605,6 +607,15 @@ __global__ void seed_goal_kernel(GridDesc d) {
     if (d.pin_x >= 0 && d.pin_x < d.EX && d.pin_y >= 0 && d.pin_y < d.EY) {
         d.g[(int64_t) d.pin_x * d.gpitch + d.pin_y] = 0.0f;
         d.seed[(d.pin_x / TS) * d.TY + (d.pin_y / TS)] = 1;
+    }
+    // further goals: in the relax mode nothing can lower a 0, in the invalidate mode a 0 is never reset, so they
+    // need no per-tile pin
+    for (int i = 0; i < d.n_xgoals; ++i) {
+        const int2 q = d.xgoals[i];
+        if (q.x >= 0 && q.x < d.EX && q.y >= 0 && q.y < d.EY) {
+            d.g[(int64_t) q.x * d.gpitch + q.y] = 0.0f;
+            d.seed[(q.x / TS) * d.TY + (q.y / TS)] = 1;
+        }
     }
 }
 

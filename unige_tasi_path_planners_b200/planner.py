@@ -132,6 +132,11 @@ class GpuPlanner:
             x, y = x
         self._check(self._L.tasi_set_goal(self._h, x, y))
 
+    def set_goals(self, goals):
+        """Several goals (sequence of (x, y)): value 0 at each, the field is the cost to the nearest one."""
+        a = np.ascontiguousarray(goals, dtype=np.float32).reshape(-1, 2)
+        self._check(self._L.tasi_set_goals(self._h, a.ctypes.data_as(C.POINTER(C.c_float)), a.shape[0]))
+
     def step(self):
         u, p = C.c_float(0), C.c_float(0)
         nu, ne = C.c_uint64(0), C.c_uint64(0)

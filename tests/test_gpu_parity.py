@@ -230,3 +230,34 @@ def test_stacked_batch_equals_single_plans(oracle, kind):
     compare(kind, sb.field(1), oracle.solve(kind, m1, goals[1]))
     compare(kind, sb.field(0), oracle.solve(kind, maps[0], goals[0]))
     sb.close()
+
+
+@pytest.mark.parametrize("kind", KINDS)
+def test_full_size_cfg2_field_is_a_fixed_point(oracle, kind):
+    """BASELINE.json's 4096 x 4096 workload: the oracle cannot solve it in seconds, but one pass of its operator over
+    the GPU field can: no element may be lowerable (residual lo == 0), for FD*/MFD* none may be raisable either
+    (a true fixed point of the reference's operator), and the reachability mask must match a flood fill."""
+    from scipy import ndimage
+    N = 4096
+    start, goal = synth.default_endpoints(N, N)
+    p = make(kind)
+    p.set_occupancy_threshold(1.0)
+    p.synth_map(1, N, N, 0, 10, start, goal)
+    p.set_start(*start)
+    p.set_goal(*goal)
+    assert p.step() == 0
+    got = p.read_field()
+    cmap = p.read_map()
+    assert np.array_equal(cmap, synth.synth_map(1, N, N, 10, start, goal))
+    lo, hi, maxrel = oracle.residual(kind, cmap, goal, got)
+    assert lo == 0
+    if kind != 1:
+        assert hi == 0
+    else:
+        assert maxrel <= 1e-6
+    # reachability: free cells 8-connected to the goal cell (MS-DFM values live on cells)
+    if kind == 1:
+        lab, _ = ndimage.label(cmap < 255, structure=np.ones((3, 3), int))
+        reach = lab == lab[int(goal[0]), int(goal[1])]
+        assert np.array_equal(np.isfinite(got), reach)
+    assert np.isfinite(got[int(start[0]), int(start[1])])

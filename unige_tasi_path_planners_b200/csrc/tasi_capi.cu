@@ -235,7 +235,9 @@ int run_solver(tasi_planner *p, int mode, float *ms, bool resume = false, float 
     CU_TRY(p, cudaMemcpyAsync(p->ctl, &z, offsetof(DevCtl, n_changed), cudaMemcpyHostToDevice, p->stream));
     CU_TRY(p, cudaEventRecord(p->ev0, p->stream));
     const int nt = p->TX * p->TY;
-    enqueue_seeds_kernel<<<std::min((nt + 255) / 256, 1024), 256, 0, p->stream>>>(d);
+    const int ordered = (mode == 0 && p->delta_factor > 0.0f) ? 1 : 0;
+    if (ordered) seed_keys_kernel<<<std::min((nt + 7) / 8, p->num_sms * 8), 256, 0, p->stream>>>(d);
+    enqueue_seeds_kernel<<<std::min((nt + 255) / 256, 1024), 256, 0, p->stream>>>(d, ordered);
     arm_solver_kernel<<<1, 1, 0, p->stream>>>(d);
     const int nblocks = (p->max_blocks > 0 && p->max_blocks < p->solver_blocks) ? p->max_blocks : p->solver_blocks;
     pick_solver(p->kind, mode)<<<nblocks, NTHREADS, 0, p->stream>>>(d);
@@ -250,7 +252,7 @@ int run_solver(tasi_planner *p, int mode, float *ms, bool resume = false, float 
     p->sv_far_count[1] = std::min(h.far_count[1], p->far_cap);
     p->sv_thr_bits = h.thr_bits;
     p->sv_far_min_bits = (p->sv_far_count[h.far_sel] > 0) ? h.far_min_bits : INF_BITS;
-    p->stats.solver_launches += 3;
+    p->stats.solver_launches += 3 + ordered;
     p->stats.queue_pushes += h.pushes;
     p->stats.phases += (uint64_t) h.phases;
     p->stats.far_parked += h.far_parked;

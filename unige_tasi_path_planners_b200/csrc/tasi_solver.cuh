@@ -620,17 +620,44 @@ __global__ void seed_goal_kernel(GridDesc d) {
 }
 
 // Move the tiles flagged in seed[] into the work queue (runs alone, before the solver).
-__global__ void enqueue_seeds_kernel(GridDesc d) {
+// One warp per flagged tile: its key becomes (at most) the lowest value it holds, so that seeded tiles enter the
+// value-ordered schedule where they belong instead of all running at once with stale inputs (a replan seeds
+// thousands of tiles; the ones nearer the goal must settle first).
+__global__ void seed_keys_kernel(GridDesc d) {
+    const int n = d.TX * d.TY, lane = threadIdx.x & 31;
+    const int nwarps = (gridDim.x * blockDim.x) >> 5;
+    for (int t = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; t < n; t += nwarps) {
+        if (!d.seed[t]) continue;
+        const int tx = t / d.TY, ty = t - tx * d.TY;
+        const float *base = d.g + (int64_t) (tx * TS) * d.gpitch + ty * TS + lane;
+        int m = INF_BITS;
+        for (int r = 0; r < TS; ++r) m = min(m, __float_as_int(__ldcg(base + (int64_t) r * d.gpitch)));  // values >= 0
+        m = __reduce_min_sync(0xffffffffu, m);
+        if (lane == 0) atomicMin(&d.key[t], m);
+    }
+}
+
+// Move the tiles flagged in seed[] into the schedule (runs alone, before the solver): into the work queue, or —
+// `ordered` — into the far pile, from where the first threshold advance releases them by key.
+__global__ void enqueue_seeds_kernel(GridDesc d, int ordered) {
     const int n = d.TX * d.TY;
+    DevCtl *c = d.ctl;
     for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < n; t += gridDim.x * blockDim.x) {
         if (d.seed[t]) {
             d.seed[t] = 0;
             // every element of a seeded tile is evaluated (all direction bits)
-            if ((atomicOr(&d.state[t], ST_DIRTY | (0x1ff << ST_SHIFT)) & ST_MASK) == 0) {
-                atomicAdd(&d.ctl->pending, 1);
-                unsigned long long s = atomicAdd(&d.ctl->tail, 1ULL);
+            const int bits = ST_DIRTY | (0x1ff << ST_SHIFT) | (ordered ? ST_FAR : 0);
+            if ((atomicOr(&d.state[t], bits) & ST_MASK) == 0) {
+                if (ordered) {
+                    const int sel = c->far_sel;
+                    const int slot = atomicAdd(&c->far_count[sel], 1);
+                    if (slot < d.far_cap) { d.far[sel * d.far_cap + slot] = t; continue; }
+                    atomicAnd(&d.state[t], ~ST_FAR);  // pile full: run it now
+                }
+                atomicAdd(&c->pending, 1);
+                unsigned long long s = atomicAdd(&c->tail, 1ULL);
                 d.queue[(unsigned) s & d.qmask] = t + 1;
-                atomicAdd(&d.ctl->pushes, 1ULL);
+                atomicAdd(&c->pushes, 1ULL);
             }
         }
     }

@@ -133,6 +133,8 @@ def _ref_lib(kind):
         R.ref_top_key.restype = C.c_float
         R.ref_top_key.argtypes = [C.c_void_p, C.POINTER(C.c_int)]
         R.ref_dump.argtypes = [C.c_void_p, _f32p, _f32p]
+        R.ref_step_costs.restype = C.c_int
+        R.ref_step_costs.argtypes = [C.c_void_p, _f32p, C.c_int]
         R.ref_extract.restype = C.c_int
         R.ref_extract.argtypes = [C.c_void_p, C.c_int, _f32p, C.c_int, C.c_int, C.c_int, _f32p, C.c_int, _f32p,
                                   _f32p, _f32p]
@@ -235,3 +237,9 @@ class RefPlanner:
                                int(allow_indirect), _p(xy, _f32p), cap, C.byref(cost), C.byref(dist),
                                C.byref(ems))
         return xy[:min(n, cap)].copy(), cost.value, dist.value, ems.value
+
+    def step_costs(self, cap=1 << 16):
+        """cost_ of the last extract(): the cost of every piece of the path."""
+        out = np.zeros(cap, np.float32)
+        n = self.R.ref_step_costs(self.h, _p(out, _f32p), cap)
+        return out[:min(n, cap)].copy()

@@ -73,6 +73,7 @@ struct IRef {
     virtual uint64_t map_size() = 0;
     virtual float top_key(int *empty) = 0;
     virtual void dump(float *g, float *rhs) = 0;
+    virtual int step_costs(float *out, int cap) = 0;
     virtual int extract(int use_field, const float *field, int max_steps, int lookahead,
                         int allow_indirect, float *xy, int cap, float *cost, float *dist,
                         float *e_ms) = 0;
@@ -164,7 +165,13 @@ struct Ref : IRef {
         *cost = extractor.total_cost;
         *dist = extractor.total_dist;
         *e_ms = extractor.e_time;
+        last_costs = extractor.cost_;
         return n;
+    }
+    std::vector<float> last_costs;
+    int step_costs(float *out, int cap) override {
+        for (int i = 0; i < (int) last_costs.size() && i < cap; ++i) out[i] = last_costs[i];
+        return (int) last_costs.size();
     }
     const uint8_t *map_bytes() override { return data.get(); }
     // the planner's own local update on caller-given neighbour values (costs come from the planner's map)
@@ -221,6 +228,8 @@ int ref_extract(void *h, int use_field, const float *field, int max_steps, int l
     return static_cast<IRef *>(h)->extract(use_field, field, max_steps, lookahead, allow_indirect, xy, cap, cost,
                                            dist, e_ms);
 }
+// cost_ of the last ref_extract (one entry per path piece)
+int ref_step_costs(void *h, float *out, int cap) { return static_cast<IRef *>(h)->step_costs(out, cap); }
 float ref_op_tri(void *h, int nx, int ny, int ax, int ay, int bx, int by, float ga, float gb) {
     return static_cast<IRef *>(h)->op_tri(nx, ny, ax, ay, bx, by, ga, gb);
 }

@@ -6,6 +6,8 @@ call raises.
 import ctypes as C
 import os
 
+import numpy as np
+
 PKG = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(PKG, "libtasi_gpu.so")
 HOSTOPS_PATH = os.path.join(PKG, "libtasi_hostops.so")
@@ -19,6 +21,7 @@ FD, DFM, MFD = 0, 1, 2
 
 _u8p = C.POINTER(C.c_uint8)
 _f32p = C.POINTER(C.c_float)
+_i32p = C.POINTER(C.c_int32)
 _u64p = C.POINTER(C.c_uint64)
 _i64p = C.POINTER(C.c_int64)
 _ip = C.POINTER(C.c_int)
@@ -112,5 +115,27 @@ def hostops():
         H.tasi_host_fd_tri_n.argtypes = [_f32p] * 5 + [C.c_long]
         H.tasi_host_mfd_tri_n.argtypes = [_f32p] * 4 + [C.c_long]
         H.tasi_host_dfm_stencil_n.argtypes = [_f32p] * 5 + [C.c_long]
+        H.tasi_host_extract.restype = C.c_int
+        H.tasi_host_extract.argtypes = [C.c_int, _f32p, _u8p, C.c_int, C.c_int, C.c_int] + [C.c_float] * 4 + \
+            [C.c_int] * 3 + [_f32p, C.c_int, _f32p, C.c_int, _i32p, _i32p, _f32p, _f32p]
         _hostops = H
     return _hostops
+
+
+def host_extract(cells, field, cmap, start, goal, thr=255, max_steps=20, lookahead=True, allow_indirect=True,
+                 cap=1 << 16):
+    """csrc/tasi_extract.cuh compiled for the host, over numpy arrays (tests only). -> (xy, piece costs, total
+    cost, total dist, status)."""
+    field = np.ascontiguousarray(field, np.float32)
+    cmap = np.ascontiguousarray(cmap, np.uint8)
+    L, W = cmap.shape
+    xy = np.zeros((cap, 2), np.float32)
+    costs = np.zeros(cap, np.float32)
+    n = np.zeros(2, np.int32)
+    tot = np.zeros(2, np.float32)
+    rc = hostops().tasi_host_extract(
+        int(cells), field.ctypes.data_as(_f32p), cmap.ctypes.data_as(_u8p), L, W, thr, start[0], start[1], goal[0],
+        goal[1], max_steps, int(lookahead), int(allow_indirect), xy.ctypes.data_as(_f32p), cap,
+        costs.ctypes.data_as(_f32p), cap, n[0:].ctypes.data_as(_i32p), n[1:].ctypes.data_as(_i32p),
+        tot[0:].ctypes.data_as(_f32p), tot[1:].ctypes.data_as(_f32p))
+    return xy[:n[0]].copy(), costs[:n[1]].copy(), float(tot[0]), float(tot[1]), rc

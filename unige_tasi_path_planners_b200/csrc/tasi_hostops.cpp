@@ -2,6 +2,7 @@
 // a C ABI so the CPU test-suite can compare them value by value with the oracle / the reference. Not used by
 // the product path: the solver evaluates the same header on the device.
 #include "tasi_update.cuh"
+#include "tasi_extract.cuh"
 
 extern "C" {
 float tasi_host_fd_tri(float g1, float g2, float b, float c) { return tasi::fd_tri(g1, g2, b, c); }
@@ -28,5 +29,20 @@ void tasi_host_mfd_tri_n(const float *g1, const float *g2, const float *c, float
 }
 void tasi_host_dfm_stencil_n(const float *ga, const float *gb, const float *tau, const float *h, float *out, long n) {
     for (long i = 0; i < n; ++i) out[i] = tasi::dfm_st(ga[i], gb[i], tau[i], h[i]);
+}
+
+// the path walk of tasi_extract.cuh over host arrays (field: row-major ex x ey floats; cost: L x W bytes)
+int tasi_host_extract(int cells, const float *field, const uint8_t *cost, int L, int W, int thr, float sx, float sy,
+                      float gx, float gy, int max_steps, int lookahead, int indirect, float *xy, int cap_points,
+                      float *costs, int cap_costs, int *n_points, int *n_costs, float *total_cost, float *total_dist) {
+    tasi::FieldView v = {field, cells ? W : W + 1, cost, W, L, W, thr, cells};
+    tasi::PathOut o = {xy, cap_points, costs, cap_costs, 0, 0, 0.0f, 0.0f};
+    const int rc = tasi::walk_path(v, tasi::SerialChooser(), sx, sy, gx, gy, max_steps, lookahead != 0,
+                                   indirect != 0, true, o);
+    *n_points = o.n_points;
+    *n_costs = o.n_costs;
+    *total_cost = o.total_cost;
+    *total_dist = o.total_dist;
+    return rc;
 }
 }

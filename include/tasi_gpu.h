@@ -164,6 +164,23 @@ int tasi_band_solve_until(tasi_planner *p, float limit, uint64_t *n_tile_visits,
 /* Width of the value band one threshold advance covers on this band's map (delta_factor * 32 * mean free cost). */
 int tasi_band_delta(tasi_planner *p, float *delta);
 
+/* ---- path extraction over the converged field ----
+ * Replaces LinearInterpolationPathExtractor::extract_path (PathExtraction/LinearInterpolationPathExtractor_impl.h:
+ * 12-58; members path_, cost_, total_cost, total_dist, lookahead, max_steps, allow_indirect_traversals of
+ * LinearInterpolationPathExtractor.h:14-22) for n independent walks over the planner's field in ONE kernel launch
+ * (one warp per walk). starts_xy / goals_xy: n (x, y) pairs; NULL = the planner's own start / goal (n must be 1).
+ * Per walk q: xy[q * cap_points * 2 ...] receives n_points[q] positions (the start first), step_costs (may be
+ * NULL) n_costs[q] piece costs, totals[2q] / totals[2q+1] the path cost and length, status[q] one of TASI_WALK_*.
+ * The reference's defaults are max_steps 20, lookahead 1, allow_indirect 1; one step adds at most 3 positions and
+ * 2 piece costs. e_ms (may be NULL): wall clock of the call, as e_time. Not available on row bands. */
+#define TASI_WALK_GOAL 0      /* the walk ended on the goal position */
+#define TASI_WALK_MAX_STEPS 1 /* max_steps steps taken (the reference keeps such a path, so do we) */
+#define TASI_WALK_STUCK 2     /* no edge around the last position can be crossed */
+#define TASI_WALK_FULL 3      /* cap_points / cap_costs reached */
+int tasi_extract_paths(tasi_planner *p, const float *starts_xy, const float *goals_xy, int n, int max_steps,
+                       int lookahead, int allow_indirect, float *xy, int cap_points, int *n_points,
+                       float *step_costs, int cap_costs, int *n_costs, float *totals, int *status, float *e_ms);
+
 #ifdef __cplusplus
 }
 #endif

@@ -14,6 +14,7 @@
 
 #include "../../include/tasi_gpu.h"
 #include "tasi_solver.cuh"
+#include "tasi_extract.cuh"
 
 using namespace tasi;
 
@@ -57,6 +58,8 @@ struct tasi_planner {
     float *stage = nullptr;  // 2 x EY receive rows (band mode)
     uint8_t *patch_buf = nullptr, *chg_buf = nullptr;
     size_t patch_cap = 0;
+    uint8_t *walk_buf = nullptr;  // queries and results of tasi_extract_paths
+    size_t walk_cap = 0;
     unsigned qsize = 0;
     int n_tiles_alloc = 0;
 
@@ -83,6 +86,11 @@ namespace {
             return TASI_ERR_CUDA;                                                                    \
         }                                                                                            \
     } while (0)
+
+inline int fail(tasi_planner *p, int code, const char *what) {
+    p->err = what;
+    return code;
+}
 
 inline bool node_based(const tasi_planner *p) { return p->kind != TASI_DFM; }
 
@@ -337,7 +345,7 @@ int tasi_destroy(tasi_planner *p) {
     cudaSetDevice(p->device);
     if (p->stream) cudaStreamSynchronize(p->stream);
     free_grid(p);
-    cudaFree(p->ctl); cudaFree(p->cost_sum); cudaFree(p->patch_buf); cudaFree(p->chg_buf); cudaFree(p->xgoals_dev);
+    cudaFree(p->ctl); cudaFree(p->cost_sum); cudaFree(p->patch_buf); cudaFree(p->chg_buf); cudaFree(p->xgoals_dev); cudaFree(p->walk_buf);
     if (p->ev0) cudaEventDestroy(p->ev0);
     if (p->ev1) cudaEventDestroy(p->ev1);
     if (p->evs0) cudaEventDestroy(p->evs0);
@@ -701,6 +709,59 @@ int tasi_band_delta(tasi_planner *p, float *delta) {
     int rc = ensure_cost_stats(p);
     if (rc != TASI_OK) return rc;
     *delta = p->delta_factor * (float) TS * p->mean_cost;
+    return TASI_OK;
+}
+
+int tasi_extract_paths(tasi_planner *p, const float *starts_xy, const float *goals_xy, int n, int max_steps,
+                       int lookahead, int allow_indirect, float *xy, int cap_points, int *n_points,
+                       float *step_costs, int cap_costs, int *n_costs, float *totals, int *status, float *e_ms) {
+    if (!p || n <= 0 || !xy || cap_points < 1 || !n_points || !totals || !status || max_steps < 1 ||
+        (step_costs && (cap_costs < 1 || !n_costs)) || ((!starts_xy || !goals_xy) && n != 1))
+        return TASI_ERR_ARG;
+    if (p->initialize_graph || p->initialize_search) return fail(p, TASI_ERR_STATE, "extract_paths: no plan yet");
+    if (p->open_top || p->open_bottom) return fail(p, TASI_ERR_STATE, "extract_paths: not available on a row band");
+    CU_TRY(p, cudaSetDevice(p->device));
+    const double t0 = now_ms();
+    std::vector<PathQuery> q((size_t) n);
+    for (int i = 0; i < n; ++i) {
+        q[i].sx = starts_xy ? starts_xy[2 * i] : p->start_x;
+        q[i].sy = starts_xy ? starts_xy[2 * i + 1] : p->start_y;
+        q[i].gx = goals_xy ? goals_xy[2 * i] : p->goal_x;
+        q[i].gy = goals_xy ? goals_xy[2 * i + 1] : p->goal_y;
+        // a walk starts inside the map (Graph::is_valid(Position), Graph.cpp:57-59)
+        if (!(q[i].sx >= 0.0f && q[i].sy >= 0.0f && q[i].sx <= (float) p->rows && q[i].sy <= (float) p->W))
+            return fail(p, TASI_ERR_ARG, "extract_paths: start outside the map");
+    }
+    // one device block: queries | xy | piece costs | n_points, n_costs, status | totals
+    const size_t capc = step_costs ? (size_t) cap_costs : 0;
+    const size_t o_q = 0, o_xy = o_q + sizeof(PathQuery) * n, o_sc = o_xy + sizeof(float) * 2 * cap_points * n,
+                 o_int = o_sc + sizeof(float) * capc * n, o_tot = o_int + sizeof(int) * 3 * n,
+                 bytes = o_tot + sizeof(float) * 2 * n;
+    if (bytes > p->walk_cap) {
+        cudaFree(p->walk_buf);
+        p->walk_buf = nullptr;
+        p->walk_cap = 0;
+        CU_TRY(p, cudaMalloc(&p->walk_buf, bytes));
+        p->walk_cap = bytes;
+    }
+    uint8_t *b = p->walk_buf;
+    CU_TRY(p, cudaMemcpyAsync(b + o_q, q.data(), sizeof(PathQuery) * n, cudaMemcpyHostToDevice, p->stream));
+    FieldView v = {g_origin(p), p->gpitch, c_origin(p), p->cpitch, p->rows, p->W, p->thr, p->kind == TASI_DFM};
+    int *ints = (int *) (b + o_int);
+    const int warps_per_block = 4;
+    extract_paths_kernel<<<(n + warps_per_block - 1) / warps_per_block, 32 * warps_per_block, 0, p->stream>>>(
+        v, (const PathQuery *) (b + o_q), n, max_steps, lookahead, allow_indirect, (float *) (b + o_xy), cap_points,
+        step_costs ? (float *) (b + o_sc) : nullptr, (int) capc, ints, ints + n, (float *) (b + o_tot), ints + 2 * n);
+    CU_TRY(p, cudaGetLastError());
+    CU_TRY(p, cudaMemcpyAsync(n_points, ints, sizeof(int) * n, cudaMemcpyDeviceToHost, p->stream));
+    if (step_costs) CU_TRY(p, cudaMemcpyAsync(n_costs, ints + n, sizeof(int) * n, cudaMemcpyDeviceToHost, p->stream));
+    CU_TRY(p, cudaMemcpyAsync(status, ints + 2 * n, sizeof(int) * n, cudaMemcpyDeviceToHost, p->stream));
+    CU_TRY(p, cudaMemcpyAsync(totals, b + o_tot, sizeof(float) * 2 * n, cudaMemcpyDeviceToHost, p->stream));
+    CU_TRY(p, cudaMemcpyAsync(xy, b + o_xy, sizeof(float) * 2 * cap_points * n, cudaMemcpyDeviceToHost, p->stream));
+    if (step_costs)
+        CU_TRY(p, cudaMemcpyAsync(step_costs, b + o_sc, sizeof(float) * capc * n, cudaMemcpyDeviceToHost, p->stream));
+    CU_TRY(p, cudaStreamSynchronize(p->stream));
+    if (e_ms) *e_ms = (float) (now_ms() - t0);
     return TASI_OK;
 }
 

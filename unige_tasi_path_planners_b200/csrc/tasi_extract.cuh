@@ -483,4 +483,92 @@ TASI_XD inline int walk_path(const FieldView &v, const Chooser &choose, float sx
     } while (!(lx == gx && ly == gy) && steps < max_steps);
     return (lx == gx && ly == gy) ? WALK_GOAL : WALK_MAX_STEPS;
 }
+
+#ifdef __CUDACC__
+// One warp per path. A position has at most 8 candidate edges and each candidate's look-ahead ring at most 8
+// more: lanes 0-7 cross the candidates, then all 32 lanes share the 64 look-ahead crossings (lane = candidate * 4
+// + quarter of its ring), and the first lowest admissible candidate is broadcast to every lane, so the warp walks
+// in lock step and lane 0 stores the path.
+struct WarpChooser {
+    __device__ bool operator()(const FieldView &v, float px, float py, bool lookahead, bool indirect, Hop &out) const {
+        const unsigned full = 0xffffffffu;
+        const int lane = threadIdx.x & 31;
+        int rx[8], ry[8];
+        const int len = ring_of(px, py, rx, ry);
+        const bool vert = is_vertex(v, px, py);
+        Hop h;
+        h.n = 0;
+        h.nc = 0;
+        h.to_goal = inf_f();
+        h.step = 0.0f;
+#pragma unroll
+        for (int i = 0; i < 3; ++i) h.x[i] = h.y[i] = 0.0f;
+        h.sc[0] = h.sc[1] = 0.0f;
+        if (lane < len) {
+            const int j = lane + 1 == len ? 0 : lane + 1;
+            if (v.node_ok(rx[lane], ry[lane]) && v.node_ok(rx[j], ry[j]))
+                hop_over_edge(v, px, py, vert, rx[lane], ry[lane], rx[j], ry[j], indirect, h);
+        }
+        const float ex = h.n ? h.x[h.n - 1] : 0.0f, ey = h.n ? h.y[h.n - 1] : 0.0f;
+        const int need = lookahead && h.n && !is_vertex(v, ex, ey);
+        const int cand = lane >> 2, quarter = lane & 3;
+        const float qx = __shfl_sync(full, ex, cand), qy = __shfl_sync(full, ey, cand);
+        const int qneed = __shfl_sync(full, need, cand);
+        float ahead = inf_f();
+        if (qneed) ahead = ring_floor(v, qx, qy, indirect, 2 * quarter, 2 * quarter + 2);
+#pragma unroll
+        for (int off = 1; off <= 2; off <<= 1) {
+            const float o = __shfl_xor_sync(full, ahead, off);
+            ahead = o < ahead ? o : ahead;
+        }
+        ahead = __shfl_sync(full, ahead, (lane * 4) & 31);
+        if (ahead == inf_f()) ahead = 0.0f;
+        const bool ok = lane < 8 && h.n && !(need && ahead > h.to_goal) && h.to_goal < inf_f();
+        const float mine = ok ? h.to_goal : inf_f();
+        float low = mine;
+#pragma unroll
+        for (int off = 16; off; off >>= 1) {
+            const float o = __shfl_xor_sync(full, low, off);
+            low = o < low ? o : low;
+        }
+        if (!(low < inf_f())) return false;
+        const int win = __ffs(__ballot_sync(full, ok && mine == low)) - 1;
+        out.n = __shfl_sync(full, h.n, win);
+        out.nc = __shfl_sync(full, h.nc, win);
+#pragma unroll
+        for (int i = 0; i < 3; ++i) {
+            out.x[i] = __shfl_sync(full, h.x[i], win);
+            out.y[i] = __shfl_sync(full, h.y[i], win);
+        }
+        out.sc[0] = __shfl_sync(full, h.sc[0], win);
+        out.sc[1] = __shfl_sync(full, h.sc[1], win);
+        out.to_goal = __shfl_sync(full, h.to_goal, win);
+        out.step = __shfl_sync(full, h.step, win);
+        return true;
+    }
+};
+
+struct PathQuery { float sx, sy, gx, gy; };
+
+__global__ void __launch_bounds__(128) extract_paths_kernel(FieldView v, const PathQuery *q, int n, int max_steps,
+                                                            int lookahead, int indirect, float *xy, int cap_points,
+                                                            float *costs, int cap_costs, int *n_points, int *n_costs,
+                                                            float *totals, int *status) {
+    const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (w >= n) return;
+    const bool writer = (threadIdx.x & 31) == 0;
+    PathOut o = {xy + (int64_t) w * cap_points * 2, cap_points, costs ? costs + (int64_t) w * cap_costs : nullptr,
+                 cap_costs, 0, 0, 0.0f, 0.0f};
+    const PathQuery pq = q[w];
+    const int rc = walk_path(v, WarpChooser(), pq.sx, pq.sy, pq.gx, pq.gy, max_steps, lookahead != 0, indirect != 0,
+                             writer, o);
+    if (writer) {
+        n_points[w] = o.n_points;
+        n_costs[w] = o.n_costs;
+        totals[2 * w] = o.total_cost;
+        totals[2 * w + 1] = o.total_dist;
+        status[w] = rc;
+    }
+}
+#endif  // __CUDACC__
 }  // namespace tasi

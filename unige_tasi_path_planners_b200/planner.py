@@ -226,6 +226,59 @@ class GpuPlanner:
         self._check(self._L.tasi_band_delta(self._h, C.byref(d)))
         return d.value
 
+    def extract_paths(self, starts=None, goals=None, max_steps=20, lookahead=True, allow_indirect=True,
+                      cap_points=None, with_costs=True):
+        """n walks over the converged field in one kernel launch (tasi_extract_paths). starts / goals: n (x, y)
+        pairs, None = the planner's own start and goal (one walk). -> list of dicts {path (k, 2), costs,
+        total_cost, total_dist, status}, plus the wall clock of the call in ms."""
+        f32p, i32p = C.POINTER(C.c_float), C.POINTER(C.c_int32)
+        if starts is None:
+            n, sp, gp = 1, None, None
+        else:
+            st = np.ascontiguousarray(starts, np.float32).reshape(-1, 2)
+            gl = np.ascontiguousarray(goals, np.float32).reshape(-1, 2)
+            assert st.shape == gl.shape
+            n, sp, gp = st.shape[0], st.ctypes.data_as(f32p), gl.ctypes.data_as(f32p)
+        cap = int(cap_points) if cap_points else 1 + 3 * max_steps
+        capc = 2 * max_steps if not cap_points else cap
+        xy = np.empty((n, cap, 2), np.float32)
+        sc = np.empty((n, capc), np.float32) if with_costs else None
+        npts, ncst, status = (np.zeros(n, np.int32) for _ in range(3))
+        totals = np.zeros((n, 2), np.float32)
+        ems = C.c_float(0)
+        self._check(self._L.tasi_extract_paths(
+            self._h, sp, gp, n, max_steps, int(lookahead), int(allow_indirect), xy.ctypes.data_as(f32p), cap,
+            npts.ctypes.data_as(i32p), sc.ctypes.data_as(f32p) if with_costs else None, capc,
+            ncst.ctypes.data_as(i32p), totals.ctypes.data_as(f32p), status.ctypes.data_as(i32p), C.byref(ems)))
+        out = [{"path": xy[i, :npts[i]].copy(), "costs": sc[i, :ncst[i]].copy() if with_costs else None,
+                "total_cost": float(totals[i, 0]), "total_dist": float(totals[i, 1]), "status": int(status[i])}
+               for i in range(n)]
+        return out, ems.value
+
+
+class PathExtractor:
+    """LinearInterpolationPathExtractor (PathExtraction/LinearInterpolationPathExtractor.h:9-22) over a GPU
+    planner: same public members, the walk runs on the device field (csrc/tasi_extract.cuh)."""
+
+    def __init__(self, planner):
+        self.planner = planner
+        self.path_ = np.zeros((0, 2), np.float32)
+        self.cost_ = np.zeros(0, np.float32)
+        self.total_cost = 0.0
+        self.total_dist = 0.0
+        self.lookahead = True
+        self.max_steps = 20
+        self.e_time = 0.0
+        self.allow_indirect_traversals = True
+        self.status = None
+
+    def extract_path(self):
+        res, self.e_time = self.planner.extract_paths(None, None, self.max_steps, self.lookahead,
+                                                      self.allow_indirect_traversals)
+        r = res[0]
+        self.path_, self.cost_ = r["path"], r["costs"]
+        self.total_cost, self.total_dist, self.status = r["total_cost"], r["total_dist"], r["status"]
+
 
 class FieldDPlanner(GpuPlanner):
     """FD* — FieldDPlanner<OPT_LVL> (FieldDStar/FieldDPlanner.h); values on nodes."""

@@ -169,6 +169,8 @@ int tasi_band_delta(tasi_planner *p, float *delta);
  * 12-58; members path_, cost_, total_cost, total_dist, lookahead, max_steps, allow_indirect_traversals of
  * LinearInterpolationPathExtractor.h:14-22) for n independent walks over the planner's field in ONE kernel launch
  * (one warp per walk). starts_xy / goals_xy: n (x, y) pairs; NULL = the planner's own start / goal (n must be 1).
+ * row_ranges (may be NULL): n (first cell row, cell rows) pairs — walk q then treats that block of rows as its
+ * whole map and its positions are relative to the block (one map of a stack planned with tasi_set_goals).
  * Per walk q: xy[q * cap_points * 2 ...] receives n_points[q] positions (the start first), step_costs (may be
  * NULL) n_costs[q] piece costs, totals[2q] / totals[2q+1] the path cost and length, status[q] one of TASI_WALK_*.
  * The reference's defaults are max_steps 20, lookahead 1, allow_indirect 1; one step adds at most 3 positions and
@@ -177,7 +179,8 @@ int tasi_band_delta(tasi_planner *p, float *delta);
 #define TASI_WALK_MAX_STEPS 1 /* max_steps steps taken (the reference keeps such a path, so do we) */
 #define TASI_WALK_STUCK 2     /* no edge around the last position can be crossed */
 #define TASI_WALK_FULL 3      /* cap_points / cap_costs reached */
-int tasi_extract_paths(tasi_planner *p, const float *starts_xy, const float *goals_xy, int n, int max_steps,
+int tasi_extract_paths(tasi_planner *p, const float *starts_xy, const float *goals_xy, const int *row_ranges, int n,
+                       int max_steps,
                        int lookahead, int allow_indirect, float *xy, int cap_points, int *n_points,
                        float *step_costs, int cap_costs, int *n_costs, float *totals, int *status, float *e_ms);
 

@@ -11,6 +11,7 @@
 // One planner family per translation unit (the reference headers share an include guard).
 #include <array>
 #include <cinttypes>
+#include <functional>
 #include <iostream>
 #include <cmath>
 #include <cstdio>
@@ -70,6 +71,7 @@ struct Drive {
     Extractor extractor;
     std::shared_ptr<uint8_t> data;
     Position next_point, goal;
+    std::function<void()> on_extract;  // runs right after extractor.extract_path(), before the rover advances
     Drive(const std::vector<uint8_t> &known, int L, int W, Position start, Position goal_, bool indirect)
         : extractor(planner.get_expanded_map(), planner.get_grid()), next_point(start), goal(goal_) {
         data = std::shared_ptr<uint8_t>(new uint8_t[known.size()], std::default_delete<uint8_t[]>());
@@ -93,6 +95,7 @@ struct Drive {
         planner.patch_map(patch, top, left, w, h);
         planner.step();
         extractor.extract_path();
+        if (on_extract) on_extract();
         if (extractor.path_.empty()) return false;
         Position prev = next_point;
         for (unsigned i = 1; i < extractor.path_.size(); i++) {
@@ -121,6 +124,11 @@ static int run(int L, int W, uint64_t seed, int max_iter, int radius) {
 #endif
     Drive<RefPlannerT<O>> ref(known, L, W, start, goal, indirect);
     Drive<GpuPlannerT<O>> gpu(known, L, W, start, goal, indirect);
+    // third arm: the device walk (tasi_extract_paths behind GpuPathExtractor) over the same GPU planner, to be
+    // compared with the reference extractor's walk over that planner's hand-off window
+    tasi_host::GpuPathExtractor<GpuPlannerT<O>> native(gpu.planner);
+    native.allow_indirect_traversals = indirect;
+    gpu.on_extract = [&native]() { native.extract_path(); };
     int bad = 0;
     for (int it = 0; it < max_iter; ++it) {
         const bool more_r = ref.iterate(world, L, W, radius);
@@ -133,8 +141,14 @@ static int run(int L, int W, uint64_t seed, int max_iter, int radius) {
         const bool same = pr.size() == pg.size() && maxd == 0.0 && more_r == more_g;
         const double cr = ref.extractor.total_cost, cg = gpu.extractor.total_cost;
         const bool cost_ok = (cr == cg) || std::fabs(cr - cg) <= 1e-3 * std::fabs(cr);
-        if (!same || !cost_ok) ++bad;
-        printf("{\"iter\": %d, \"ref_points\": %zu, \"gpu_points\": %zu, \"max_point_diff\": %.9g, \"ref_cost\": %.9g, "
+        bool native_same = native.path_.size() == pg.size() && native.total_cost == gpu.extractor.total_cost &&
+                           native.total_dist == gpu.extractor.total_dist && native.cost_ == gpu.extractor.cost_;
+        for (size_t i = 0; native_same && i < pg.size(); ++i)
+            native_same = native.path_[i].x == pg[i].x && native.path_[i].y == pg[i].y;
+        if (!same || !cost_ok || !native_same) ++bad;
+        printf("{\"iter\": %d, \"device_walk_identical\": %s, \"device_walk_ms\": %.3f, \"ref_walk_ms\": %.3f,",
+               it, native_same ? "true" : "false", native.e_time, ref.extractor.e_time);
+        printf(" \"it\": %d, \"ref_points\": %zu, \"gpu_points\": %zu, \"max_point_diff\": %.9g, \"ref_cost\": %.9g, "
                "\"gpu_cost\": %.9g, \"ref_pos\": [%.6g, %.6g], \"gpu_pos\": [%.6g, %.6g], \"identical\": %s, "
                "\"ref_ms\": [%.3f, %.3f], \"gpu_ms\": [%.3f, %.3f], \"ref_expanded\": %lu, \"gpu_updated\": %lu}\n",
                it, pr.size(), pg.size(), maxd, cr, cg, ref.next_point.x, ref.next_point.y, gpu.next_point.x,

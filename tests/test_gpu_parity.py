@@ -220,6 +220,17 @@ def test_stacked_batch_equals_single_plans(oracle, kind):
     w = sb.window(2, -5, 10, 20, 30)
     f = sb.field(2)
     assert np.all(np.isinf(w[:5])) and np.array_equal(w[5:], f[0:15, 10:40])
+    # one walk per query in one launch == the walk over each block's own field (rows at the seams included)
+    from unige_tasi_path_planners_b200 import _lib
+    starts = [(0.0, 0.0), (69.0, 99.0), (70.0, 50.0), (2.5, 60.0)]
+    for m, s in zip(maps, starts):
+        synth.clear_block(m, int(s[0]), int(s[1]))
+    sb.plan(maps, goals)
+    walks, _ = sb.paths(starts, 2000, with_costs=True)
+    for i, (m, s, g) in enumerate(zip(maps, starts, goals)):
+        hw = _lib.host_extract(kind == 1, sb.field(i), m, s, g, 255, 2000)
+        assert np.array_equal(walks[i]["path"], hw[0]) and np.array_equal(walks[i]["costs"], hw[1]), i
+        assert walks[i]["status"] == hw[4] and (kind == 1 or hw[4] == 0)
     # a replan on the stack: patch map 1's block, every block still equals its own from-scratch plan
     patch = synth.synth_rows(77, 0, 20, 30, 20)
     sb.p.patch_map(patch, 1 * (L + 1) + 10, 40)

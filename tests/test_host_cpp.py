@@ -87,6 +87,13 @@ def test_plan_demo_matches_oracle(demo, oracle, kind, tmp_path):
             assert (np.abs(got[m] - want[m]) / np.maximum(want[m], 1e-30)).max() <= 1e-4
         else:
             assert np.array_equal(got[m], want[m])
+        # GpuPathExtractor (device walk, reference defaults) == the same walk on the host over the dumped field
+        from unige_tasi_path_planners_b200 import _lib
+        path = np.fromfile(dump + "." + what + ".path", np.float32).reshape(-1, 2)
+        hw = _lib.host_extract(k == 1, got, cm, start if what == "plan" else (8.0, 8.0), goal, 255, 20)
+        assert np.array_equal(path, hw[0])
+        line = lines[0 if what == "plan" else 1]
+        assert line["path_points"] == len(path) and line["path_cost"] == pytest.approx(hw[2], rel=1e-6)
     assert lines[1]["num_nodes_updated"] > 0 and lines[0]["tile_visits"] > 0
     # FieldMap hand-off: get_rhs(start element) is the field value there
     ex = (5, 5)
@@ -105,6 +112,8 @@ def test_reference_extractor_and_demo_loop_over_gpu_planner(kind, level):
     assert lines, r.stderr
     steps = [l for l in lines if "iter" in l]
     assert len(steps) >= 5
+    # third arm: the device walk (GpuPathExtractor) equals the reference extractor's walk over the same GPU field
+    assert all(s["device_walk_identical"] for s in steps)
     if kind == "dfm":
         # MS-DFM fields agree to ~1e-7, not bit for bit, and the extractor's edge interpolation amplifies an ulp
         # into ~1e-3 of a cell: same number of points, each within 0.05 cell, path cost within 1e-3 (north_star)

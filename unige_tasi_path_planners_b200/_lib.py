@@ -74,7 +74,7 @@ SIGNATURES = {
     "tasi_band_solve": (C.c_int, [C.c_void_p, _u64p]),
     "tasi_band_solve_until": (C.c_int, [C.c_void_p, C.c_float, _u64p, _f32p]),
     "tasi_band_delta": (C.c_int, [C.c_void_p, _f32p]),
-    "tasi_extract_paths": (C.c_int, [C.c_void_p, _f32p, _f32p, C.c_int, C.c_int, C.c_int, C.c_int, _f32p, C.c_int,
+    "tasi_extract_paths": (C.c_int, [C.c_void_p, _f32p, _f32p, _i32p, C.c_int, C.c_int, C.c_int, C.c_int, _f32p, C.c_int,
                                      _i32p, _f32p, C.c_int, _i32p, _f32p, _i32p, _f32p]),
 }
 

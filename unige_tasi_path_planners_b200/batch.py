@@ -88,6 +88,7 @@ class StackedBatch:
         self.p.set_map(stack_maps(maps))
         off = self.L + 1
         self.p.set_start(0.0, 0.0)
+        self.goals = [tuple(g) for g in goals]
         self.p.set_goals([(g[0] + i * off, g[1]) for i, g in enumerate(goals)])
         rc = self.p.step()
         assert rc == 0, rc
@@ -107,6 +108,15 @@ class StackedBatch:
         if xa < xb:
             w[xa - x0:xb - x0] = self.p.read_window(i * (self.L + 1) + xa, y0, xb - xa, ny)
         return w
+
+    def paths(self, starts, max_steps=20, lookahead=True, allow_indirect=True, with_costs=False):
+        """One walk per query from its start to its goal (map coordinates), all in one kernel launch; each
+        walk sees only its own block of rows (row_ranges), so it is the walk a planner holding only that map gives."""
+        n = len(self.goals)
+        rr = [(i * (self.L + 1), self.L) for i in range(n)]
+        res, ms = self.p.extract_paths(starts, self.goals, max_steps, lookahead, allow_indirect,
+                                       with_costs=with_costs, row_ranges=rr)
+        return res, ms
 
     def close(self):
         self.p.close()
@@ -136,18 +146,28 @@ def bench_main(args, rank, world):
             sb = StackedBatch(kind, 1, local)
             buf = np.empty((64, 64), np.float32)
 
+            walk_steps = int(os.environ.get("TASI_BATCH_WALK_STEPS", "20"))  # 0 = fields and windows only
+            walk = {"ms": 0.0, "points": 0, "at_goal": 0}
+
             def run_chunks(qs):
                 reached = launches = 0
                 for c0 in range(0, len(qs), chunk):
                     part = qs[c0:c0 + chunk]
                     sb.plan([host_maps[q[0]] for q in part], [q[2] for q in part])
                     launches += sb.p.stats()["solver_launches"]
+                    if walk_steps:
+                        res, ms = sb.paths([q[1] for q in part], walk_steps)
+                        walk["ms"] += ms
+                        walk["points"] += sum(len(r["path"]) for r in res)
+                        walk["at_goal"] += sum(r["status"] == 0 for r in res)
+                        launches += 1
                     for i, q in enumerate(part):
                         sb.window(i, int(q[1][0]) - 32, int(q[1][1]) - 32, 64, 64, out=buf)
                         reached += bool(np.isfinite(buf[32, 32]))
                 return reached, launches
 
             run_chunks(mine[:8])  # warm-up
+            walk.update(ms=0.0, points=0, at_goal=0)
             torch.cuda.synchronize()
             if world > 1:
                 dist.barrier()
@@ -164,7 +184,9 @@ def bench_main(args, rank, world):
             results[name] = {"queries": int(cnt[0]), "reached": int(cnt[1]), "seconds": float(tm[0]),
                              "queries_per_s": int(cnt[0]) / float(tm[0]),
                              "mcells_per_s": int(cnt[0]) * side * side / float(tm[0]) / 1e6,
-                             "gpu_launches": int(cnt[2])}
+                             "gpu_launches": int(cnt[2]),
+                             "walks": {"max_steps": walk_steps, "ms_total_rank0": walk["ms"],
+                                       "points_rank0": walk["points"], "at_goal_rank0": walk["at_goal"]}}
             continue
         maps = sorted({q[0] for q in mine})
         lane_q = [[q for q in mine if maps.index(q[0]) % lanes == l] for l in range(lanes)]
@@ -208,7 +230,8 @@ def bench_main(args, rank, world):
                        "lanes_per_gpu": lanes, "solver_ctas_per_lane": max(1, 444 // lanes),
                        "sharding": "whole maps per rank, no collective on the data path",
                        "timing": "wall clock of the whole batch: H2D of the (stacked) maps from host memory, goal "
-                                 "upload, plan and D2H of the 64x64 hand-off window per query; max over ranks"},
+                                 "upload, plan, one device walk per query (TASI_BATCH_WALK_STEPS, default 20 steps as the "
+                                 "reference extractor) and D2H of the 64x64 hand-off window per query; max over ranks"},
             "per_planner": results}), flush=True)
     if world > 1:
         dist.destroy_process_group()

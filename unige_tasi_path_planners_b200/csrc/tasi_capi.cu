@@ -58,7 +58,7 @@ struct tasi_planner {
     float *stage = nullptr;  // 2 x EY receive rows (band mode)
     uint8_t *patch_buf = nullptr, *chg_buf = nullptr;
     size_t patch_cap = 0;
-    uint8_t *walk_buf = nullptr;  // queries and results of tasi_extract_paths
+    uint8_t *walk_buf = nullptr, *walk_host = nullptr;  // queries and results of tasi_extract_paths (device, pinned)
     size_t walk_cap = 0;
     unsigned qsize = 0;
     int n_tiles_alloc = 0;
@@ -345,7 +345,7 @@ int tasi_destroy(tasi_planner *p) {
     cudaSetDevice(p->device);
     if (p->stream) cudaStreamSynchronize(p->stream);
     free_grid(p);
-    cudaFree(p->ctl); cudaFree(p->cost_sum); cudaFree(p->patch_buf); cudaFree(p->chg_buf); cudaFree(p->xgoals_dev); cudaFree(p->walk_buf);
+    cudaFree(p->ctl); cudaFree(p->cost_sum); cudaFree(p->patch_buf); cudaFree(p->chg_buf); cudaFree(p->xgoals_dev); cudaFree(p->walk_buf); cudaFreeHost(p->walk_host);
     if (p->ev0) cudaEventDestroy(p->ev0);
     if (p->ev1) cudaEventDestroy(p->ev1);
     if (p->evs0) cudaEventDestroy(p->evs0);
@@ -712,8 +712,8 @@ int tasi_band_delta(tasi_planner *p, float *delta) {
     return TASI_OK;
 }
 
-int tasi_extract_paths(tasi_planner *p, const float *starts_xy, const float *goals_xy, int n, int max_steps,
-                       int lookahead, int allow_indirect, float *xy, int cap_points, int *n_points,
+int tasi_extract_paths(tasi_planner *p, const float *starts_xy, const float *goals_xy, const int *row_ranges, int n,
+                       int max_steps, int lookahead, int allow_indirect, float *xy, int cap_points, int *n_points,
                        float *step_costs, int cap_costs, int *n_costs, float *totals, int *status, float *e_ms) {
     if (!p || n <= 0 || !xy || cap_points < 1 || !n_points || !totals || !status || max_steps < 1 ||
         (step_costs && (cap_costs < 1 || !n_costs)) || ((!starts_xy || !goals_xy) && n != 1))
@@ -728,39 +728,51 @@ int tasi_extract_paths(tasi_planner *p, const float *starts_xy, const float *goa
         q[i].sy = starts_xy ? starts_xy[2 * i + 1] : p->start_y;
         q[i].gx = goals_xy ? goals_xy[2 * i] : p->goal_x;
         q[i].gy = goals_xy ? goals_xy[2 * i + 1] : p->goal_y;
+        q[i].row0 = row_ranges ? row_ranges[2 * i] : 0;
+        q[i].rows = row_ranges ? row_ranges[2 * i + 1] : 0;
+        if (row_ranges && (q[i].row0 < 0 || q[i].rows < 1 || q[i].row0 + q[i].rows > p->rows))
+            return fail(p, TASI_ERR_ARG, "extract_paths: row range outside the map");
+        const int rows = row_ranges ? q[i].rows : p->rows;
         // a walk starts inside the map (Graph::is_valid(Position), Graph.cpp:57-59)
-        if (!(q[i].sx >= 0.0f && q[i].sy >= 0.0f && q[i].sx <= (float) p->rows && q[i].sy <= (float) p->W))
+        if (!(q[i].sx >= 0.0f && q[i].sy >= 0.0f && q[i].sx <= (float) rows && q[i].sy <= (float) p->W))
             return fail(p, TASI_ERR_ARG, "extract_paths: start outside the map");
     }
-    // one device block: queries | xy | piece costs | n_points, n_costs, status | totals
+    // one device block: queries | n_points, n_costs, status | totals | xy | piece costs; everything after the
+    // queries comes back in ONE copy into a pinned staging block and is scattered to the caller's arrays here
     const size_t capc = step_costs ? (size_t) cap_costs : 0;
-    const size_t o_q = 0, o_xy = o_q + sizeof(PathQuery) * n, o_sc = o_xy + sizeof(float) * 2 * cap_points * n,
-                 o_int = o_sc + sizeof(float) * capc * n, o_tot = o_int + sizeof(int) * 3 * n,
-                 bytes = o_tot + sizeof(float) * 2 * n;
+    const size_t o_int = sizeof(PathQuery) * n, o_tot = o_int + sizeof(int) * 3 * n, o_xy = o_tot + sizeof(float) * 2 * n,
+                 o_sc = o_xy + sizeof(float) * 2 * cap_points * n, bytes = o_sc + sizeof(float) * capc * n;
     if (bytes > p->walk_cap) {
         cudaFree(p->walk_buf);
-        p->walk_buf = nullptr;
+        cudaFreeHost(p->walk_host);
+        p->walk_buf = p->walk_host = nullptr;
         p->walk_cap = 0;
         CU_TRY(p, cudaMalloc(&p->walk_buf, bytes));
+        CU_TRY(p, cudaHostAlloc(&p->walk_host, bytes, cudaHostAllocDefault));
         p->walk_cap = bytes;
     }
-    uint8_t *b = p->walk_buf;
-    CU_TRY(p, cudaMemcpyAsync(b + o_q, q.data(), sizeof(PathQuery) * n, cudaMemcpyHostToDevice, p->stream));
+    uint8_t *b = p->walk_buf, *hb = p->walk_host;
+    if (n > 1) {
+        memcpy(hb, q.data(), sizeof(PathQuery) * n);
+        CU_TRY(p, cudaMemcpyAsync(b, hb, sizeof(PathQuery) * n, cudaMemcpyHostToDevice, p->stream));
+    }
     FieldView v = {g_origin(p), p->gpitch, c_origin(p), p->cpitch, p->rows, p->W, p->thr, p->kind == TASI_DFM};
     int *ints = (int *) (b + o_int);
     const int warps_per_block = 4;
     extract_paths_kernel<<<(n + warps_per_block - 1) / warps_per_block, 32 * warps_per_block, 0, p->stream>>>(
-        v, (const PathQuery *) (b + o_q), n, max_steps, lookahead, allow_indirect, (float *) (b + o_xy), cap_points,
-        step_costs ? (float *) (b + o_sc) : nullptr, (int) capc, ints, ints + n, (float *) (b + o_tot), ints + 2 * n);
+        v, n > 1 ? (const PathQuery *) b : nullptr, q[0], n, max_steps, lookahead, allow_indirect, (float *) (b + o_xy),
+        cap_points, step_costs ? (float *) (b + o_sc) : nullptr, (int) capc, ints, ints + n, (float *) (b + o_tot),
+        ints + 2 * n);
     CU_TRY(p, cudaGetLastError());
-    CU_TRY(p, cudaMemcpyAsync(n_points, ints, sizeof(int) * n, cudaMemcpyDeviceToHost, p->stream));
-    if (step_costs) CU_TRY(p, cudaMemcpyAsync(n_costs, ints + n, sizeof(int) * n, cudaMemcpyDeviceToHost, p->stream));
-    CU_TRY(p, cudaMemcpyAsync(status, ints + 2 * n, sizeof(int) * n, cudaMemcpyDeviceToHost, p->stream));
-    CU_TRY(p, cudaMemcpyAsync(totals, b + o_tot, sizeof(float) * 2 * n, cudaMemcpyDeviceToHost, p->stream));
-    CU_TRY(p, cudaMemcpyAsync(xy, b + o_xy, sizeof(float) * 2 * cap_points * n, cudaMemcpyDeviceToHost, p->stream));
-    if (step_costs)
-        CU_TRY(p, cudaMemcpyAsync(step_costs, b + o_sc, sizeof(float) * capc * n, cudaMemcpyDeviceToHost, p->stream));
+    CU_TRY(p, cudaMemcpyAsync(hb + o_int, b + o_int, bytes - o_int, cudaMemcpyDeviceToHost, p->stream));
     CU_TRY(p, cudaStreamSynchronize(p->stream));
+    const int *hi = (const int *) (hb + o_int);
+    memcpy(n_points, hi, sizeof(int) * n);
+    if (step_costs) memcpy(n_costs, hi + n, sizeof(int) * n);
+    memcpy(status, hi + 2 * n, sizeof(int) * n);
+    memcpy(totals, hb + o_tot, sizeof(float) * 2 * n);
+    memcpy(xy, hb + o_xy, sizeof(float) * 2 * cap_points * n);
+    if (step_costs) memcpy(step_costs, hb + o_sc, sizeof(float) * capc * n);
     if (e_ms) *e_ms = (float) (now_ms() - t0);
     return TASI_OK;
 }

@@ -548,9 +548,13 @@ struct WarpChooser {
     }
 };
 
-struct PathQuery { float sx, sy, gx, gy; };
+// row0 / rows: the walk sees only cell rows row0 .. row0 + rows - 1 as its map, in coordinates relative to row0
+// (rows == 0: the whole map) — one block of a stack of independent maps (tasi_set_goals)
+struct PathQuery { float sx, sy, gx, gy; int row0, rows; };
 
-__global__ void __launch_bounds__(128) extract_paths_kernel(FieldView v, const PathQuery *q, int n, int max_steps,
+// q == nullptr: one walk, its query travels in the launch arguments (q0)
+__global__ void __launch_bounds__(128) extract_paths_kernel(FieldView v, const PathQuery *q, PathQuery q0, int n,
+                                                            int max_steps,
                                                             int lookahead, int indirect, float *xy, int cap_points,
                                                             float *costs, int cap_costs, int *n_points, int *n_costs,
                                                             float *totals, int *status) {
@@ -559,7 +563,12 @@ __global__ void __launch_bounds__(128) extract_paths_kernel(FieldView v, const P
     const bool writer = (threadIdx.x & 31) == 0;
     PathOut o = {xy + (int64_t) w * cap_points * 2, cap_points, costs ? costs + (int64_t) w * cap_costs : nullptr,
                  cap_costs, 0, 0, 0.0f, 0.0f};
-    const PathQuery pq = q[w];
+    const PathQuery pq = q ? q[w] : q0;
+    if (pq.rows > 0) {
+        v.g += (int64_t) pq.row0 * v.gpitch;
+        v.cost += (int64_t) pq.row0 * v.cpitch;
+        v.L = pq.rows;
+    }
     const int rc = walk_path(v, WarpChooser(), pq.sx, pq.sy, pq.gx, pq.gy, max_steps, lookahead != 0, indirect != 0,
                              writer, o);
     if (writer) {

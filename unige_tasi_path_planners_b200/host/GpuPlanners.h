@@ -340,6 +340,47 @@ class GpuReplanner {
     ElemT goal_elem_;
 };
 
+// ---- the extractor surface -------------------------------------------------------------------------------------
+// LinearInterpolationPathExtractor (PathExtraction/LinearInterpolationPathExtractor.h:9-22) with the walk on the
+// device: same public members; bound to the planner instead of to its (map, grid) pair, because the field never
+// leaves the GPU. One extract_path() = one launch of the warp-per-walk kernel (tasi_extract_paths) and one D2H of
+// the positions;
+// the hand-off window of reference-types mode is not read on this route.
+template <typename Planner>
+class GpuPathExtractor {
+ public:
+    explicit GpuPathExtractor(Planner &planner) : planner_(planner) {}
+
+    void extract_path() {
+        const int cap = 1 + 3 * max_steps, capc = 2 * max_steps;
+        std::vector<float> xy((size_t) cap * 2), sc((size_t) capc);
+        int np = 0, nc = 0;
+        float totals[2] = {0, 0};
+        const int rc = tasi_extract_paths(planner_.handle(), nullptr, nullptr, nullptr, 1, max_steps, lookahead ? 1 : 0,
+                                          allow_indirect_traversals ? 1 : 0, xy.data(), cap, &np, sc.data(), capc, &nc,
+                                          totals, &status, &e_time);
+        if (rc != TASI_OK) throw GpuError(rc, std::string("tasi_extract_paths: ") + planner_.last_error());
+        path_.clear();
+        cost_.assign(sc.begin(), sc.begin() + nc);
+        for (int i = 0; i < np; ++i) path_.push_back(Position(xy[2 * i], xy[2 * i + 1]));
+        total_cost = totals[0];
+        total_dist = totals[1];
+    }
+
+    std::vector<Position> path_{};
+    std::vector<float> cost_{};
+    float total_cost = 0;
+    float total_dist = 0;
+    bool lookahead = true;
+    int max_steps = 20;
+    float e_time = 0;
+    bool allow_indirect_traversals = true;
+    int status = TASI_WALK_GOAL;  // extra: why the walk ended (TASI_WALK_*)
+
+ private:
+    Planner &planner_;
+};
+
 }  // namespace tasi_host
 
 template <int OptimizationLevel>

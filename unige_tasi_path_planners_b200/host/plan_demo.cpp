@@ -47,17 +47,26 @@ void report(Planner &pl, const char *what, const std::string &dump) {
         if (v < std::numeric_limits<float>::infinity()) { sum += v; ++fin; }
     const tasi_stats st = pl.stats();
     const auto &grid = pl.get_grid();
+    // the demo loop's extractor.extract_path() (FDSTAR/main.cpp:116), on the device
+    tasi_host::GpuPathExtractor<Planner> ex(pl);
+    ex.extract_path();
     typename Planner::Elem se(grid.start_pos_);
     printf("{\"step\": \"%s\", \"u_time\": %.4f, \"p_time\": %.4f, \"num_nodes_updated\": %lu, \"num_nodes_expanded\": %lu, "
            "\"finite\": %" PRIu64 ", \"sum\": %.9g, \"start_value\": %.9g, \"start_interp_rhs\": %.9g, "
-           "\"tile_visits\": %" PRIu64 ", \"kernel_ms_solve\": %.4f, \"kernel_ms_inval\": %.4f}\n",
+           "\"tile_visits\": %" PRIu64 ", \"kernel_ms_solve\": %.4f, \"kernel_ms_inval\": %.4f, "
+           "\"path_points\": %zu, \"path_cost\": %.9g, \"path_dist\": %.9g, \"path_status\": %d, \"e_time\": %.4f}\n",
            what, pl.u_time, pl.p_time, pl.num_nodes_updated, pl.num_nodes_expanded, fin, sum,
            pl.get_expanded_map().get_rhs(se),
            pl.get_expanded_map().get_interp_rhs(tasi_host::Node(grid.start_pos_)), st.tile_visits,
-           st.kernel_ms_solve, st.kernel_ms_inval);
+           st.kernel_ms_solve, st.kernel_ms_inval, ex.path_.size(), ex.total_cost, ex.total_dist, ex.status, ex.e_time);
     if (!dump.empty()) {
         FILE *fp = fopen((dump + "." + what).c_str(), "wb");
         if (fp) { fwrite(f.data(), sizeof(float), f.size(), fp); fclose(fp); }
+        fp = fopen((dump + "." + what + ".path").c_str(), "wb");
+        if (fp) {
+            for (const auto &q : ex.path_) { fwrite(&q.x, sizeof(float), 1, fp); fwrite(&q.y, sizeof(float), 1, fp); }
+            fclose(fp);
+        }
     }
 }
 

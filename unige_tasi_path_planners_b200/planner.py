@@ -227,9 +227,10 @@ class GpuPlanner:
         return d.value
 
     def extract_paths(self, starts=None, goals=None, max_steps=20, lookahead=True, allow_indirect=True,
-                      cap_points=None, with_costs=True):
+                      cap_points=None, with_costs=True, row_ranges=None):
         """n walks over the converged field in one kernel launch (tasi_extract_paths). starts / goals: n (x, y)
-        pairs, None = the planner's own start and goal (one walk). -> list of dicts {path (k, 2), costs,
+        pairs, None = the planner's own start and goal (one walk). row_ranges: n (first cell row, cell rows) pairs —
+        each walk sees that block of rows as its whole map, positions relative to the block. -> list of dicts {path (k, 2), costs,
         total_cost, total_dist, status}, plus the wall clock of the call in ms."""
         f32p, i32p = C.POINTER(C.c_float), C.POINTER(C.c_int32)
         if starts is None:
@@ -239,6 +240,11 @@ class GpuPlanner:
             gl = np.ascontiguousarray(goals, np.float32).reshape(-1, 2)
             assert st.shape == gl.shape
             n, sp, gp = st.shape[0], st.ctypes.data_as(f32p), gl.ctypes.data_as(f32p)
+        rr = None
+        if row_ranges is not None:
+            rr_a = np.ascontiguousarray(row_ranges, np.int32).reshape(-1, 2)
+            assert rr_a.shape[0] == n
+            rr = rr_a.ctypes.data_as(i32p)
         cap = int(cap_points) if cap_points else 1 + 3 * max_steps
         capc = 2 * max_steps if not cap_points else cap
         xy = np.empty((n, cap, 2), np.float32)
@@ -247,7 +253,7 @@ class GpuPlanner:
         totals = np.zeros((n, 2), np.float32)
         ems = C.c_float(0)
         self._check(self._L.tasi_extract_paths(
-            self._h, sp, gp, n, max_steps, int(lookahead), int(allow_indirect), xy.ctypes.data_as(f32p), cap,
+            self._h, sp, gp, rr, n, max_steps, int(lookahead), int(allow_indirect), xy.ctypes.data_as(f32p), cap,
             npts.ctypes.data_as(i32p), sc.ctypes.data_as(f32p) if with_costs else None, capc,
             ncst.ctypes.data_as(i32p), totals.ctypes.data_as(f32p), status.ctypes.data_as(i32p), C.byref(ems)))
         out = [{"path": xy[i, :npts[i]].copy(), "costs": sc[i, :ncst[i]].copy() if with_costs else None,

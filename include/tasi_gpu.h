@@ -62,6 +62,8 @@ typedef struct tasi_stats {
      * tile, staging it, relaxing it, writing back + activating neighbours */
     uint64_t cyc_pop, cyc_stage, cyc_relax, cyc_post;
     uint64_t cyc_advance;      /* cycles one CTA spent advancing the threshold while all others waited */
+    float settled_below;       /* every field value below this is final; +INF = the whole field is (no focus) */
+    int focus_hit;             /* the last plan ended because the start was settled (tasi_set_focus) */
 } tasi_stats;
 
 /* Planner object. kind = TASI_FD|TASI_DFM|TASI_MFD; level = the reference's OPT_LVL template argument
@@ -163,6 +165,17 @@ int tasi_band_solve(tasi_planner *p, uint64_t *n_tile_visits);
 int tasi_band_solve_until(tasi_planner *p, float limit, uint64_t *n_tile_visits, float *next_key);
 /* Width of the value band one threshold advance covers on this band's map (delta_factor * 32 * mean free cost). */
 int tasi_band_delta(tasi_planner *p, float *delta);
+
+/* ---- focused planning ----
+ * The reference's plan() stops once the start is settled (end_condition: FieldDPlanner_impl.h:225-256 waits for the
+ * four corner nodes of the start cell, DynamicFastMarching_impl.h:315-320 for the start cell; the shifted-grid
+ * planner as FD*). With enabled != 0, step() does the same: the solver's value-ordered schedule ends the launch as
+ * soon as every value up to (highest finite value among those elements) + slack is final; tiles with later work
+ * stay parked and the next step() — after a patch, a new start, or focus switched off — resumes them. Values at or
+ * above tasi_stats.settled_below may still be upper bounds (as the reference's are beyond its queue's top key).
+ * slack < 0 = default (4 * 254: covers every node within two cells of the start cell, what the extractor's first
+ * step reads). Off by default: step() then converges the whole field. Not available on row bands. */
+int tasi_set_focus(tasi_planner *p, int enabled, float slack);
 
 /* ---- path extraction over the converged field ----
  * Replaces LinearInterpolationPathExtractor::extract_path (PathExtraction/LinearInterpolationPathExtractor_impl.h:

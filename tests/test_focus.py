@@ -1,0 +1,155 @@
+"""Focused planning (tasi_set_focus): step() stops once the start is settled, as the reference's
+end_condition does (FieldDPlanner_impl.h:225-256, DynamicFastMarching_impl.h:315-320), later work stays parked and
+is resumed by the following steps.
+
+What must hold: every value below stats.settled_below equals the converged field of the current map (bit-exact for
+FD*/MFD*, 1e-4 for MS-DFM), everything else is an upper bound of it, the start's elements are among the settled
+ones, the walk from the start equals the walk over the fully converged field, and switching focus off completes
+the field exactly.
+"""
+import numpy as np
+import pytest
+
+from unige_tasi_path_planners_b200 import _lib, synth
+
+pytestmark = pytest.mark.gpu
+KINDS = [0, 1, 2]
+
+
+def make(kind):
+    from unige_tasi_path_planners_b200 import PLANNERS
+    p = PLANNERS[kind](1)
+    p.set_occupancy_threshold(1.0)
+    return p
+
+
+def start_elems(kind, start):
+    cx, cy = int(np.floor(start[0] + 0.5)), int(np.floor(start[1] + 0.5))
+    return [(cx, cy)] if kind == 1 else [(cx, cy), (cx, cy + 1), (cx + 1, cy), (cx + 1, cy + 1)]
+
+
+def check_settled(kind, got, want, settled_below, start):
+    m = want < settled_below
+    assert np.array_equal(np.isfinite(got[m]), np.isfinite(want[m]))
+    if kind == 1:
+        assert (np.abs(got[m] - want[m]) / np.maximum(want[m], 1e-30)).max(initial=0.0) <= 1e-4
+    else:
+        assert np.array_equal(got[m], want[m]), "%d settled values differ" % (got[m] != want[m]).sum()
+    # nothing anywhere lies below the converged value (unsettled values are upper bounds)
+    fin = np.isfinite(want)
+    assert np.all(got[fin] >= want[fin] * (1 - 1e-5 if kind == 1 else 1.0))
+    assert np.all(np.isinf(got[~fin]))
+    top = max((want[e] for e in start_elems(kind, start) if np.isfinite(want[e])), default=None)
+    assert top is not None and top < settled_below
+    return int(m.sum())
+
+
+@pytest.mark.parametrize("kind", KINDS)
+def test_focused_plan_settles_up_to_the_start_and_resumes(oracle, kind):
+    L = W = 384
+    goal, start = (300.0, 300.0), (262.0, 275.0)
+    cmap = synth.synth_map(21, L, W, 10, start, goal)
+    want = oracle.solve(kind, cmap, goal)
+    full = make(kind)
+    full.set_map(cmap); full.set_start(*start); full.set_goal(*goal)
+    assert full.step() == 0
+    full_visits = full.stats()["tile_visits"]
+    full.close()
+
+    p = make(kind)
+    p.set_focus(True)
+    p.set_map(cmap); p.set_start(*start); p.set_goal(*goal)
+    assert p.step() == 0
+    st = p.stats()
+    assert st["focus_hit"] == 1 and np.isfinite(st["settled_below"])
+    assert st["tile_visits"] < 0.6 * full_visits
+    n = check_settled(kind, p.read_field(), want, st["settled_below"], start)
+    assert 0 < n < want.size / 2
+    # the walk from the start reads settled values only where it matters: same walk as over the converged field
+    res, _ = p.extract_paths(None, None, 20)
+    hw = _lib.host_extract(kind == 1, want, cmap, start, goal, 255, 20)
+    if kind != 1:
+        assert np.array_equal(res[0]["path"], hw[0])
+    assert res[0]["total_cost"] == pytest.approx(hw[2], rel=1e-3)
+    # a farther start with no map change: the parked work resumes up to the new start
+    far = (120.0, 90.0)
+    p.set_start(*far)
+    assert p.step() == 0
+    st2 = p.stats()
+    assert st2["settled_below"] > st["settled_below"]
+    got = p.read_field()
+    want0 = want
+    if np.isfinite(want0[start_elems(kind, far)[0]]):
+        check_settled(kind, got, want0, st2["settled_below"], far)
+    # focus off: the next step completes the field
+    p.set_focus(False)
+    p.set_start(*far)
+    assert p.step() == 0
+    st3 = p.stats()
+    assert np.isinf(st3["settled_below"]) and st3["focus_hit"] == 0
+    got = p.read_field()
+    fin = np.isfinite(want0)
+    assert np.array_equal(np.isfinite(got), fin)
+    if kind == 1:
+        assert (np.abs(got[fin] - want0[fin]) / np.maximum(want0[fin], 1e-30)).max() <= 1e-4
+    else:
+        assert np.array_equal(got[fin], want0[fin])
+    p.close()
+
+
+@pytest.mark.parametrize("kind", KINDS)
+def test_focused_demo_loop_with_patches(oracle, kind):
+    """The demo loop (FDSTAR/main.cpp:111-166): the rover reveals a patch of the true world around itself, replans,
+    advances along the extracted path — here with focus on and raise + lower patches at every step."""
+    L, W = 200, 240
+    start, goal = (6.0, 6.0), (150.0, 200.0)
+    world = synth.synth_map(33, L, W, 12, start, goal)
+    known = np.full((L, W), 20, np.uint8)
+    p = make(kind)
+    p.set_focus(True)
+    p.set_map(known); p.set_start(*start); p.set_goal(*goal)
+    pos = start
+    radius = 7
+    moved = 0
+    for it in range(12):
+        cx, cy = int(round(pos[0])), int(round(pos[1]))
+        x0, y0 = max(cx - radius, 0), max(cy - radius, 0)
+        x1, y1 = min(cx + radius + 1, L), min(cy + radius + 1, W)
+        patch = world[x0:x1, y0:y1].copy()
+        patch[max(cx - 1 - x0, 0):cx + 2 - x0, max(cy - 1 - y0, 0):cy + 2 - y0] = 5  # the rover's own cells stay free
+        known[x0:x1, y0:y1] = patch
+        p.patch_map(patch, x0, y0)
+        p.set_start(*pos)
+        assert p.step() == 0
+        st = p.stats()
+        want = oracle.solve(kind, known, goal)
+        if not np.isfinite(want[start_elems(kind, pos)[0]]):
+            break
+        check_settled(kind, p.read_field(), want, st["settled_below"], pos)
+        res, _ = p.extract_paths(None, None, 20)
+        hw = _lib.host_extract(kind == 1, want, known, pos, goal, 255, 20)
+        if kind != 1:
+            assert np.array_equal(res[0]["path"], hw[0]), "iteration %d" % it
+        assert res[0]["total_cost"] == pytest.approx(hw[2], rel=1e-3)
+        path = res[0]["path"]
+        if len(path) < 2:
+            break
+        nxt = pos
+        for q in path[1:]:
+            nxt = (float(q[0]), float(q[1]))
+            if np.hypot(round(nxt[0]) - round(pos[0]), round(nxt[1]) - round(pos[1])) > 5:
+                break
+        moved += nxt != pos
+        pos = nxt
+    assert moved >= 8
+    p.set_focus(False)
+    p.set_start(*pos)
+    assert p.step() == 0
+    got, want = p.read_field(), oracle.solve(kind, known, goal)
+    fin = np.isfinite(want)
+    assert np.array_equal(np.isfinite(got), fin)
+    if kind == 1:
+        assert (np.abs(got[fin] - want[fin]) / np.maximum(want[fin], 1e-30)).max() <= 1e-4
+    else:
+        assert np.array_equal(got[fin], want[fin])
+    p.close()

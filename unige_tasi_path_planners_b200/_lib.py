@@ -36,7 +36,8 @@ class Stats(C.Structure):
                 ("solver_blocks", C.c_int32),
                 ("solver_launches", C.c_int32),
                 ("cyc_pop", C.c_uint64), ("cyc_stage", C.c_uint64), ("cyc_relax", C.c_uint64),
-                ("cyc_post", C.c_uint64), ("cyc_advance", C.c_uint64)]
+                ("cyc_post", C.c_uint64), ("cyc_advance", C.c_uint64),
+                ("settled_below", C.c_float), ("focus_hit", C.c_int)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}
@@ -74,6 +75,7 @@ SIGNATURES = {
     "tasi_band_solve": (C.c_int, [C.c_void_p, _u64p]),
     "tasi_band_solve_until": (C.c_int, [C.c_void_p, C.c_float, _u64p, _f32p]),
     "tasi_band_delta": (C.c_int, [C.c_void_p, _f32p]),
+    "tasi_set_focus": (C.c_int, [C.c_void_p, C.c_int, C.c_float]),
     "tasi_extract_paths": (C.c_int, [C.c_void_p, _f32p, _f32p, _i32p, C.c_int, C.c_int, C.c_int, C.c_int, _f32p, C.c_int,
                                      _i32p, _f32p, C.c_int, _i32p, _f32p, _i32p, _f32p]),
 }

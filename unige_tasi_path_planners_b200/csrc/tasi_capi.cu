@@ -68,6 +68,10 @@ struct tasi_planner {
     uint64_t last_seed_count = 0;
 
     int solver_blocks = 0, max_blocks = 0;
+    // focused planning (tasi_set_focus): plans stop once the start is settled, the rest stays parked
+    bool focus = false;
+    float focus_slack = 4.0f * 254.0f;
+    bool pile_open = false;  // a focused plan left parked tiles: the field is final only below settled_below
     // band mode: the parked tiles and the threshold survive from one launch to the next
     bool band_started = false;
     int sv_far_sel = 0, sv_far_count[2] = {0, 0}, sv_thr_bits = 0, sv_far_min_bits = INF_BITS;
@@ -116,6 +120,18 @@ GridDesc make_desc(const tasi_planner *p) {
     d.key = p->key; d.far = p->far; d.far_cap = p->far_cap;
     d.delta = p->delta_factor * (float) TS * p->mean_cost;
     d.inval_tol = (p->kind == TASI_DFM) ? 1e-6f : 0.0f;
+    d.n_focus = 0;
+    d.focus_slack = p->focus_slack;
+    if (p->focus && !p->open_top && !p->open_bottom) {
+        // Graph::set_start: start_cell_ = Cell(start) rounds (Cell.cpp:20-21); FD*/MFD* wait for the cell's four
+        // corner nodes (FieldDPlanner_impl.h:12, Cell.cpp:58-60), MS-DFM for the cell itself
+        const int cx = (int) roundf(p->start_x), cy = (int) roundf(p->start_y);
+        const int n = p->kind == TASI_DFM ? 1 : 4;
+        for (int i = 0; i < n; ++i) {
+            const int x = cx + (i >> 1), y = cy + (i & 1);
+            if (x >= 0 && y >= 0 && x < p->EX && y < p->EY) d.focus[d.n_focus++] = make_int2(x, y);
+        }
+    }
     return d;
 }
 
@@ -227,6 +243,7 @@ int run_solver(tasi_planner *p, int mode, float *ms, bool resume = false, float 
     int rcs = ensure_cost_stats(p);
     if (rcs != TASI_OK) return rcs;
     GridDesc d = make_desc(p);
+    if (mode == 1) d.n_focus = 0;
     DevCtl z;
     memset(&z, 0, sizeof z);
     z.timeout_ns = (unsigned long long) (p->timeout_s * 1e9);
@@ -237,7 +254,7 @@ int run_solver(tasi_planner *p, int mode, float *ms, bool resume = false, float 
         z.far_sel = p->sv_far_sel;
         z.far_count[0] = p->sv_far_count[0];
         z.far_count[1] = p->sv_far_count[1];
-        z.thr_bits = p->sv_thr_bits;
+        z.thr_bits = (mode == 1) ? INF_BITS : p->sv_thr_bits;
     }
     // reset queue tickets + per-launch counters, keep the patch bookkeeping
     CU_TRY(p, cudaMemcpyAsync(p->ctl, &z, offsetof(DevCtl, n_changed), cudaMemcpyHostToDevice, p->stream));
@@ -260,6 +277,11 @@ int run_solver(tasi_planner *p, int mode, float *ms, bool resume = false, float 
     p->sv_far_count[1] = std::min(h.far_count[1], p->far_cap);
     p->sv_thr_bits = h.thr_bits;
     p->sv_far_min_bits = (p->sv_far_count[h.far_sel] > 0) ? h.far_min_bits : INF_BITS;
+    if (mode == 0) {
+        p->pile_open = p->sv_far_count[h.far_sel] > 0 && !p->open_top && !p->open_bottom;
+        p->stats.focus_hit = h.focus_hit;
+        memcpy(&p->stats.settled_below, &p->sv_far_min_bits, sizeof(float));
+    }
     p->stats.solver_launches += 3 + ordered;
     p->stats.queue_pushes += h.pushes;
     p->stats.phases += (uint64_t) h.phases;
@@ -543,7 +565,8 @@ int tasi_step(tasi_planner *p, float *u_ms, float *p_ms, uint64_t *n_updated, ui
             p->last_seed_count = hc.n_seed_elems;
             // phase 1 of the repair: raised costs may have left values without support
             if (hc.n_raised > 0) {
-                rc = run_solver(p, 1, &ms);
+                // tiles parked by a focused plan keep their place: the invalidate launch never releases them
+                rc = run_solver(p, 1, &ms, p->pile_open, p->pile_open ? 0.0f : INFINITY);
                 if (rc != TASI_OK) return rc;
                 p->stats.kernel_ms_inval = ms;
             }
@@ -558,8 +581,12 @@ int tasi_step(tasi_planner *p, float *u_ms, float *p_ms, uint64_t *n_updated, ui
     }
     double t1 = now_ms();
 
-    if (p->new_goal || p->initialize_search || p->num_nodes_updated > 0) {  // ReplannerBase.h:64-69 -> plan()
-        rc = run_solver(p, 0, &ms);
+    const bool fresh = p->initialize_search || p->new_goal;
+    if (fresh) p->pile_open = false;
+    // ReplannerBase.h:64-69 -> plan(); also whenever a focused plan left work parked (the new start may lie beyond
+    // what is settled)
+    if (fresh || p->num_nodes_updated > 0 || p->pile_open) {
+        rc = run_solver(p, 0, &ms, p->pile_open);
         if (rc != TASI_OK) return rc;
         p->stats.kernel_ms_solve = ms;
         p->num_nodes_expanded = p->stats.elem_lowered;
@@ -567,6 +594,7 @@ int tasi_step(tasi_planner *p, float *u_ms, float *p_ms, uint64_t *n_updated, ui
         p->num_nodes_expanded = 0;
     }
     p->new_goal = p->initialize_search = false;
+    if (!p->pile_open) p->stats.settled_below = INFINITY;
     CU_TRY(p, cudaEventRecord(p->evs1, p->stream));
     CU_TRY(p, cudaEventSynchronize(p->evs1));
     CU_TRY(p, cudaEventElapsedTime(&p->stats.step_ms_device, p->evs0, p->evs1));
@@ -774,6 +802,13 @@ int tasi_extract_paths(tasi_planner *p, const float *starts_xy, const float *goa
     memcpy(xy, hb + o_xy, sizeof(float) * 2 * cap_points * n);
     if (step_costs) memcpy(step_costs, hb + o_sc, sizeof(float) * capc * n);
     if (e_ms) *e_ms = (float) (now_ms() - t0);
+    return TASI_OK;
+}
+
+int tasi_set_focus(tasi_planner *p, int enabled, float slack) {
+    if (!p) return TASI_ERR_ARG;
+    p->focus = enabled != 0;
+    p->focus_slack = slack >= 0.0f ? slack : 4.0f * 254.0f;
     return TASI_OK;
 }
 

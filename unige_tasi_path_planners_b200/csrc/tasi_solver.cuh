@@ -56,6 +56,8 @@ struct DevCtl {
     unsigned long long evals;       // element evaluations
     unsigned long long cyc_pop, cyc_stage, cyc_relax, cyc_post;  // SM cycles summed over CTAs (thread 0's clock)
     unsigned long long cyc_advance;  // cycles the advancing CTA spent raising the threshold (all others wait)
+    int focus_hit;                  // the launch ended because the focus elements were settled (work stays parked)
+    int pad0;
     // patch bookkeeping
     unsigned long long n_changed, n_raised, n_lowered_cells, n_seed_elems;
     unsigned long long halo_lowered;
@@ -83,6 +85,11 @@ struct GridDesc {
     float delta;           // width of the value band processed per phase
     DevCtl *ctl;
     float inval_tol;       // relative slack of the invalidate test (0 for FD*/MFD*)
+    // focused plan (the reference's end_condition, FieldDPlanner_impl.h:225-256, DynamicFastMarching_impl.h:315-320):
+    // the launch ends once every value up to the highest finite one among these elements (+ slack) is final
+    int n_focus;           // 0 = solve to convergence
+    int2 focus[4];         // the start cell's corner nodes / the start cell, local coordinates
+    float focus_slack;
 };
 
 // Release/acquire fence at device scope. __threadfence() compiles to the sequentially consistent MEMBAR.SC.GPU;
@@ -199,6 +206,19 @@ __device__ inline bool advance_threshold(const GridDesc &d, int *s_red, int tid)
     const int lim = *(volatile int *) &c->limit_bits;
     if (tid == 0) c->far_min_bits = m;
     if (m != INF_BITS && m >= lim) return true;
+    if (d.n_focus > 0 && m != INF_BITS) {
+        // the queue is empty and every parked key is >= m: all values below m are final. Values only depend on
+        // lower ones, so the focus elements are settled once the highest finite one lies below m.
+        float top = -1.0f;
+        for (int i = 0; i < d.n_focus; ++i) {
+            const float v = __ldcg(d.g + (int64_t) d.focus[i].x * d.gpitch + d.focus[i].y);
+            if (v < __int_as_float(INF_BITS)) top = fmaxf(top, v);
+        }
+        if (top >= 0.0f && top + d.focus_slack < __int_as_float(m)) {
+            if (tid == 0) c->focus_hit = 1;
+            return true;
+        }
+    }
     int nthr = INF_BITS;
     if (m != INF_BITS) {
         const float t = __int_as_float(m) + d.delta;
@@ -647,7 +667,16 @@ __global__ void enqueue_seeds_kernel(GridDesc d, int ordered) {
             d.seed[t] = 0;
             // every element of a seeded tile is evaluated (all direction bits)
             const int bits = ST_DIRTY | (0x1ff << ST_SHIFT) | (ordered ? ST_FAR : 0);
-            if ((atomicOr(&d.state[t], bits) & ST_MASK) == 0) {
+            const int old = atomicOr(&d.state[t], bits) & ST_MASK;
+            if (!ordered && (old & ST_FAR)) {
+                // parked by an earlier focused plan: this launch (the invalidate phase) runs it now, its pile
+                // entry goes stale
+                atomicAnd(&d.state[t], ~ST_FAR);
+                atomicAdd(&c->pending, 1);
+                unsigned long long s = atomicAdd(&c->tail, 1ULL);
+                d.queue[(unsigned) s & d.qmask] = t + 1;
+                atomicAdd(&c->pushes, 1ULL);
+            } else if (old == 0) {
                 if (ordered) {
                     const int sel = c->far_sel;
                     const int slot = atomicAdd(&c->far_count[sel], 1);

@@ -274,6 +274,10 @@ class GpuReplanner {
     const Map &get_expanded_map() { return map; }
     const HostGrid &get_grid() { return grid; }
 
+    // the reference's plan() always stops once the start is settled (end_condition); here it is a switch, off by
+    // default (the whole field converges). slack < 0 = default
+    void set_focus(bool enabled, float slack = -1.0f) { check(tasi_set_focus(h_, enabled ? 1 : 0, slack), "tasi_set_focus"); }
+
     // ---- beyond the reference: device-side evidence and bulk access ------------------------------------------
     tasi_stats stats() const { tasi_stats s; tasi_get_stats(h_, &s); return s; }
     const char *last_error() const { return tasi_last_error(h_); }

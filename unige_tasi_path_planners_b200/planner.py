@@ -226,6 +226,11 @@ class GpuPlanner:
         self._check(self._L.tasi_band_delta(self._h, C.byref(d)))
         return d.value
 
+    def set_focus(self, enabled=True, slack=-1.0):
+        """Plans stop once the start is settled (the reference's end_condition); later work stays parked and is
+        resumed by the next step(). slack < 0 = default."""
+        self._check(self._L.tasi_set_focus(self._h, int(bool(enabled)), float(slack)))
+
     def extract_paths(self, starts=None, goals=None, max_steps=20, lookahead=True, allow_indirect=True,
                       cap_points=None, with_costs=True, row_ranges=None):
         """n walks over the converged field in one kernel launch (tasi_extract_paths). starts / goals: n (x, y)

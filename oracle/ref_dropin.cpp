@@ -109,7 +109,7 @@ struct Drive {
 };
 
 template <int O>
-static int run(int L, int W, uint64_t seed, int max_iter, int radius) {
+static int run(int L, int W, uint64_t seed, int max_iter, int radius, bool focus) {
     std::vector<uint8_t> world, known((size_t) L * W, 20);
     make_world(world, L, W, seed, 10);
     const Position start(5.0f, 5.0f), goal((float) (L - 6), (float) (W - 6));
@@ -126,6 +126,7 @@ static int run(int L, int W, uint64_t seed, int max_iter, int radius) {
     Drive<GpuPlannerT<O>> gpu(known, L, W, start, goal, indirect);
     // third arm: the device walk (tasi_extract_paths behind GpuPathExtractor) over the same GPU planner, to be
     // compared with the reference extractor's walk over that planner's hand-off window
+    gpu.planner.set_focus(focus);  // the reference always stops at the start (end_condition); ours on request
     tasi_host::GpuPathExtractor<GpuPlannerT<O>> native(gpu.planner);
     native.allow_indirect_traversals = indirect;
     gpu.on_extract = [&native]() { native.extract_path(); };
@@ -162,15 +163,16 @@ static int run(int L, int W, uint64_t seed, int max_iter, int radius) {
 
 int main(int argc, char **argv) {
     if (argc < 6) {
-        fprintf(stderr, "usage: %s <level> <length> <width> <seed> <max_iter> [radius]\n", argv[0]);
+        fprintf(stderr, "usage: %s <level> <length> <width> <seed> <max_iter> [radius] [focus 0|1]\n", argv[0]);
         return 64;
     }
     const int level = atoi(argv[1]), L = atoi(argv[2]), W = atoi(argv[3]);
     const uint64_t seed = strtoull(argv[4], nullptr, 10);
     const int max_iter = atoi(argv[5]), radius = argc > 6 ? atoi(argv[6]) : 5;
+    const bool focus = argc > 7 && atoi(argv[7]) != 0;
     try {
-        if (level == 0) return run<0>(L, W, seed, max_iter, radius);
-        return run<1>(L, W, seed, max_iter, radius);
+        if (level == 0) return run<0>(L, W, seed, max_iter, radius, focus);
+        return run<1>(L, W, seed, max_iter, radius, focus);
     } catch (const std::exception &e) {
         fprintf(stderr, "ref_dropin: %s\n", e.what());
         return 70;

@@ -71,8 +71,23 @@ def build_host_demo(force=False):
     return HOST_DEMO
 
 
+FIFO_DEMO = os.path.join(HOST_DIR, "fifo_demo")
+
+
+def build_fifo_demo(force=False):
+    """host/fifo_demo.cpp: the demos' planner process (FIFO wire protocol) over the GPU planners."""
+    srcs = [os.path.join(HOST_DIR, "fifo_demo.cpp"), os.path.join(HOST_DIR, "GpuPlanners.h"),
+            os.path.join(PKG, "..", "include", "tasi_gpu.h"), LIB]
+    if force or _stale(FIFO_DEMO, srcs):
+        subprocess.check_call(["g++", "-std=c++17", "-O2", "-Wall", "-I", os.path.join(PKG, "..", "include"), "-I", HOST_DIR,
+                               os.path.join(HOST_DIR, "fifo_demo.cpp"), "-L", PKG, "-ltasi_gpu",
+                               "-Wl,-rpath,$ORIGIN/..", "-o", FIFO_DEMO])
+    return FIFO_DEMO
+
+
 if __name__ == "__main__":
     import sys
     build(force="--force" in sys.argv, verbose="-v" in sys.argv)
     build_host_demo(force="--force" in sys.argv)
+    build_fifo_demo(force="--force" in sys.argv)
     print(LIB)

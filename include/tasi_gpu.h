@@ -177,6 +177,16 @@ int tasi_band_delta(tasi_planner *p, float *delta);
  * step reads). Off by default: step() then converges the whole field. Not available on row bands. */
 int tasi_set_focus(tasi_planner *p, int enabled, float slack);
 
+/* ---- parent (back-pointer) field ----
+ * What the reference's level-1 planners keep as INFO next to (g, rhs): for FD* / MFD* the node b whose triangle
+ * (b, ccw(b)) gave the value (FieldDPlanner_impl.h:91-95, 196-208), for MS-DFM the (lower, higher) cells of the winning
+ * stencil (DynamicFastMarching_impl.h:322-342). Computed on demand from the field for the window (x0, y0, nx, ny), which
+ * must lie inside the field: out receives nx * ny * 4 signed bytes (dx1, dy1, dx2, dy2) = offsets of the two parents
+ * (FD* / MFD*: b and ccw(b)); (0, 0) = absent (goals, unreached elements, one-sided MS-DFM updates). Among triangles
+ * that tie, the last in the order of Graph::neighbors_8 is reported (min_rhs<1>); the reference's own choice among
+ * ties depends on its expansion order. */
+int tasi_read_parents(tasi_planner *p, int x0, int y0, int nx, int ny, signed char *out);
+
 /* ---- path extraction over the converged field ----
  * Replaces LinearInterpolationPathExtractor::extract_path (PathExtraction/LinearInterpolationPathExtractor_impl.h:
  * 12-58; members path_, cost_, total_cost, total_dist, lookahead, max_steps, allow_indirect_traversals of

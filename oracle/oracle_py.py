@@ -133,6 +133,8 @@ def _ref_lib(kind):
         R.ref_top_key.restype = C.c_float
         R.ref_top_key.argtypes = [C.c_void_p, C.POINTER(C.c_int)]
         R.ref_dump.argtypes = [C.c_void_p, _f32p, _f32p]
+        R.ref_dump_info.restype = C.c_int
+        R.ref_dump_info.argtypes = [C.c_void_p, C.POINTER(C.c_int32)]
         R.ref_step_costs.restype = C.c_int
         R.ref_step_costs.argtypes = [C.c_void_p, _f32p, C.c_int]
         R.ref_extract.restype = C.c_int
@@ -237,6 +239,14 @@ class RefPlanner:
                                int(allow_indirect), _p(xy, _f32p), cap, C.byref(cost), C.byref(dist),
                                C.byref(ems))
         return xy[:min(n, cap)].copy(), cost.value, dist.value, ems.value
+
+    def dump_info(self):
+        """INFO (level-1 back-pointers) of every expanded element: (ex, ey, 4) int32, INT32_MIN = absent.
+        FD*/MFD*: [..., :2] = the node b of the triangle (b, ccw(b)); MS-DFM: the two parent cells."""
+        shape = field_shape(self.kind, self.L, self.W)
+        out = np.empty(shape + (4,), np.int32)
+        have = self.R.ref_dump_info(self.h, out.ctypes.data_as(C.POINTER(C.c_int32)))
+        return out if have else None
 
     def step_costs(self, cap=1 << 16):
         """cost_ of the last extract(): the cost of every piece of the path."""

@@ -74,6 +74,7 @@ struct IRef {
     virtual float top_key(int *empty) = 0;
     virtual void dump(float *g, float *rhs) = 0;
     virtual int step_costs(float *out, int cap) = 0;
+    virtual int dump_info(int32_t *out) = 0;
     virtual int extract(int use_field, const float *field, int max_steps, int lookahead,
                         int allow_indirect, float *xy, int cap, float *cost, float *dist,
                         float *e_ms) = 0;
@@ -81,6 +82,23 @@ struct IRef {
     virtual float op_tri(int nx, int ny, int ax, int ay, int bx, int by, float ga, float gb) = 0;
     virtual float op_stencil(float ga, float gb, float tau, float h) = 0;
 };
+
+// INFO of an expanded element (the level-1 back-pointers): a Node for FD*/MFD* (the first node of the triangle
+// (b, ccw(b)) that gave rhs, FieldDPlanner_impl.h:91-95), a pair of Cells for MS-DFM (DynamicFastMarching_impl.h:
+// 322-342); level 0 keeps none (two-element tuples: the variadic overload answers 0)
+static void put_info(const Node &n, int32_t *o) { o[0] = n.x; o[1] = n.y; o[2] = o[3] = INT32_MIN; }
+static void put_info(const std::pair<Cell, Cell> &p, int32_t *o) {
+    o[0] = p.first.x; o[1] = p.first.y; o[2] = p.second.x; o[3] = p.second.y;
+}
+template<typename Tuple>
+static typename std::enable_if<std::tuple_size<Tuple>::value == 3, int>::type info_of(const Tuple &t, int32_t *o) {
+    put_info(std::get<2>(t), o);
+    return 1;
+}
+template<typename Tuple>
+static typename std::enable_if<std::tuple_size<Tuple>::value != 3, int>::type info_of(const Tuple &, int32_t *) {
+    return 0;
+}
 
 template<int O>
 struct Ref : IRef {
@@ -137,6 +155,18 @@ struct Ref : IRef {
                 g[i] = std::get<0>(kv.second);
                 rhs[i] = std::get<1>(kv.second);
             }
+    }
+    int dump_info(int32_t *out) override {
+        size_t n = (size_t) ex() * ey();
+        for (size_t i = 0; i < 4 * n; ++i) out[i] = INT32_MIN;
+        int have = 0;
+        for (auto &b : planner.map.buckets)
+            for (auto &kv : b) {
+                const Elem &e = kv.first;
+                if (e.x < 0 || e.y < 0 || e.x >= ex() || e.y >= ey()) continue;
+                have |= info_of(kv.second, out + 4 * ((size_t) e.x * ey() + e.y));
+            }
+        return have;
     }
     int extract(int use_field, const float *field, int max_steps, int lookahead, int allow_indirect,
                 float *xy, int cap, float *cost, float *dist, float *e_ms) override {
@@ -228,6 +258,8 @@ int ref_extract(void *h, int use_field, const float *field, int max_steps, int l
     return static_cast<IRef *>(h)->extract(use_field, field, max_steps, lookahead, allow_indirect, xy, cap, cost,
                                            dist, e_ms);
 }
+// INFO of every expanded element as 4 int32 (INT32_MIN = absent); returns 0 when the level keeps no INFO
+int ref_dump_info(void *h, int32_t *out) { return static_cast<IRef *>(h)->dump_info(out); }
 // cost_ of the last ref_extract (one entry per path piece)
 int ref_step_costs(void *h, float *out, int cap) { return static_cast<IRef *>(h)->step_costs(out, cap); }
 float ref_op_tri(void *h, int nx, int ny, int ax, int ay, int bx, int by, float ga, float gb) {

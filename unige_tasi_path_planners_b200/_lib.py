@@ -75,6 +75,7 @@ SIGNATURES = {
     "tasi_band_solve": (C.c_int, [C.c_void_p, _u64p]),
     "tasi_band_solve_until": (C.c_int, [C.c_void_p, C.c_float, _u64p, _f32p]),
     "tasi_band_delta": (C.c_int, [C.c_void_p, _f32p]),
+    "tasi_read_parents": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),
     "tasi_set_focus": (C.c_int, [C.c_void_p, C.c_int, C.c_float]),
     "tasi_extract_paths": (C.c_int, [C.c_void_p, _f32p, _f32p, _i32p, C.c_int, C.c_int, C.c_int, C.c_int, _f32p, C.c_int,
                                      _i32p, _f32p, C.c_int, _i32p, _f32p, _i32p, _f32p]),
@@ -122,8 +123,31 @@ def hostops():
         H.tasi_host_extract.restype = C.c_int
         H.tasi_host_extract.argtypes = [C.c_int, _f32p, _u8p, C.c_int, C.c_int, C.c_int] + [C.c_float] * 4 + \
             [C.c_int] * 3 + [_f32p, C.c_int, _f32p, C.c_int, _i32p, _i32p, _f32p, _f32p]
+        H.tasi_host_node_triangles.argtypes = [C.c_int, _f32p, _u8p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _f32p]
+        H.tasi_host_parents.argtypes = [C.c_int, _f32p, _u8p, C.c_int, C.c_int, C.c_int, C.c_void_p]
         _hostops = H
     return _hostops
+
+
+def host_node_triangles(kind, field, cmap, x, y, thr=255):
+    """The 8 triangle values of node (x, y) in the order of Graph::neighbors_8 (tests only)."""
+    field = np.ascontiguousarray(field, np.float32)
+    cmap = np.ascontiguousarray(cmap, np.uint8)
+    out = np.zeros(8, np.float32)
+    hostops().tasi_host_node_triangles(int(kind), field.ctypes.data_as(_f32p), cmap.ctypes.data_as(_u8p), cmap.shape[0],
+                                       cmap.shape[1], thr, int(x), int(y), out.ctypes.data_as(_f32p))
+    return out
+
+
+def host_parents(kind, field, cmap, thr=255):
+    """csrc/tasi_parents.cuh compiled for the host (tests only): (ex, ey, 4) int8 offsets of the two parents."""
+    field = np.ascontiguousarray(field, np.float32)
+    cmap = np.ascontiguousarray(cmap, np.uint8)
+    L, W = cmap.shape
+    out = np.zeros(field.shape + (4,), np.int8)
+    hostops().tasi_host_parents(int(kind), field.ctypes.data_as(_f32p), cmap.ctypes.data_as(_u8p), L, W, thr,
+                                out.ctypes.data_as(C.c_void_p))
+    return out
 
 
 def host_extract(cells, field, cmap, start, goal, thr=255, max_steps=20, lookahead=True, allow_indirect=True,

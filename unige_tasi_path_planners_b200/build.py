@@ -49,7 +49,7 @@ def build(force=False, verbose=False):
 def build_hostops(force=False):
     """The local updates of csrc/tasi_update.cuh compiled for the host (operator-level tests only)."""
     srcs = [os.path.join(CSRC, "tasi_hostops.cpp"), os.path.join(CSRC, "tasi_update.cuh"),
-            os.path.join(CSRC, "tasi_extract.cuh")]
+            os.path.join(CSRC, "tasi_extract.cuh"), os.path.join(CSRC, "tasi_parents.cuh")]
     if force or _stale(HOSTLIB, srcs):
         subprocess.check_call(["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-fPIC", "-shared", "-o", HOSTLIB,
                                os.path.join(CSRC, "tasi_hostops.cpp")])

@@ -15,6 +15,7 @@
 #include "../../include/tasi_gpu.h"
 #include "tasi_solver.cuh"
 #include "tasi_extract.cuh"
+#include "tasi_parents.cuh"
 
 using namespace tasi;
 
@@ -809,6 +810,35 @@ int tasi_set_focus(tasi_planner *p, int enabled, float slack) {
     if (!p) return TASI_ERR_ARG;
     p->focus = enabled != 0;
     p->focus_slack = slack >= 0.0f ? slack : 4.0f * 254.0f;
+    return TASI_OK;
+}
+
+int tasi_read_parents(tasi_planner *p, int x0, int y0, int nx, int ny, signed char *out) {
+    if (!p || !out || nx <= 0 || ny <= 0 || p->initialize_graph) return TASI_ERR_ARG;
+    if (x0 < 0 || y0 < 0 || x0 + nx > p->EX || y0 + ny > p->EY) return fail(p, TASI_ERR_ARG, "read_parents: window outside the field");
+    if (p->initialize_search) return fail(p, TASI_ERR_STATE, "read_parents: no plan yet");
+    CU_TRY(p, cudaSetDevice(p->device));
+    const size_t bytes = (size_t) nx * ny * sizeof(Parents);
+    if (bytes > p->walk_cap) {  // shares the staging block of tasi_extract_paths
+        cudaFree(p->walk_buf);
+        cudaFreeHost(p->walk_host);
+        p->walk_buf = p->walk_host = nullptr;
+        p->walk_cap = 0;
+        CU_TRY(p, cudaMalloc(&p->walk_buf, bytes));
+        CU_TRY(p, cudaHostAlloc(&p->walk_host, bytes, cudaHostAllocDefault));
+        p->walk_cap = bytes;
+    }
+    const int blocks = (int) std::min<int64_t>(((int64_t) nx * ny + 255) / 256, (int64_t) p->num_sms * 16);
+    Parents *dev = (Parents *) p->walk_buf;
+    if (p->kind == TASI_FD)
+        parents_kernel<TASI_KIND_FD><<<blocks, 256, 0, p->stream>>>(g_origin(p), p->gpitch, c_origin(p), p->cpitch, p->thr, x0, y0, nx, ny, dev);
+    else if (p->kind == TASI_DFM)
+        parents_kernel<TASI_KIND_DFM><<<blocks, 256, 0, p->stream>>>(g_origin(p), p->gpitch, c_origin(p), p->cpitch, p->thr, x0, y0, nx, ny, dev);
+    else
+        parents_kernel<TASI_KIND_MFD><<<blocks, 256, 0, p->stream>>>(g_origin(p), p->gpitch, c_origin(p), p->cpitch, p->thr, x0, y0, nx, ny, dev);
+    CU_TRY(p, cudaGetLastError());
+    CU_TRY(p, cudaMemcpyAsync(out, dev, bytes, cudaMemcpyDeviceToHost, p->stream));
+    CU_TRY(p, cudaStreamSynchronize(p->stream));
     return TASI_OK;
 }
 

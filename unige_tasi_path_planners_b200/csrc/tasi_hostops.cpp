@@ -3,6 +3,7 @@
 // the product path: the solver evaluates the same header on the device.
 #include "tasi_update.cuh"
 #include "tasi_extract.cuh"
+#include "tasi_parents.cuh"
 
 extern "C" {
 float tasi_host_fd_tri(float g1, float g2, float b, float c) { return tasi::fd_tri(g1, g2, b, c); }
@@ -44,5 +45,45 @@ int tasi_host_extract(int cells, const float *field, const uint8_t *cost, int L,
     *total_cost = o.total_cost;
     *total_dist = o.total_dist;
     return rc;
+}
+
+// the parent field of tasi_parents.cuh over host arrays (field: ex x ey floats; cost: L x W bytes); out: ex*ey*4 bytes
+void tasi_host_parents(int kind, const float *field, const uint8_t *cost, int L, int W, int thr, signed char *out) {
+    const bool cells = kind == TASI_KIND_DFM;
+    const int ex = cells ? L : L + 1, ey = cells ? W : W + 1;
+    auto G = [&](int x, int y) { return (x < 0 || y < 0 || x >= ex || y >= ey) ? INFINITY : field[(size_t) x * ey + y]; };
+    auto C = [&](int x, int y) {
+        if (x < 0 || y < 0 || x >= L || y >= W) return (float) INFINITY;
+        const int v = cost[(size_t) x * W + y];
+        return v >= thr ? (float) INFINITY : (float) v;
+    };
+    for (int x = 0; x < ex; ++x)
+        for (int y = 0; y < ey; ++y) {
+            const tasi::Nbr8 g = {G(x - 1, y), G(x + 1, y), G(x, y - 1), G(x, y + 1),
+                                  G(x - 1, y - 1), G(x - 1, y + 1), G(x + 1, y - 1), G(x + 1, y + 1)};
+            const tasi::Parents p = cells ? tasi::cell_parents(g, C(x, y), G(x, y))
+                                          : tasi::node_parents(kind, g, C(x - 1, y - 1), C(x - 1, y), C(x, y - 1), C(x, y), G(x, y));
+            signed char *o = out + 4 * ((size_t) x * ey + y);
+            o[0] = p.dx1; o[1] = p.dy1; o[2] = p.dx2; o[3] = p.dy2;
+        }
+}
+
+// the 8 triangle values of node (x, y) in the order of Graph::neighbors_8 (triangle k = (b_k, ccw(b_k))), for the tests
+void tasi_host_node_triangles(int kind, const float *field, const uint8_t *cost, int L, int W, int thr, int x, int y,
+                              float *out) {
+    const int ex = L + 1, ey = W + 1;
+    auto G = [&](int a, int b) { return (a < 0 || b < 0 || a >= ex || b >= ey) ? INFINITY : field[(size_t) a * ey + b]; };
+    auto C = [&](int a, int b) {
+        if (a < 0 || b < 0 || a >= L || b >= W) return (float) INFINITY;
+        const int v = cost[(size_t) a * W + b];
+        return v >= thr ? (float) INFINITY : (float) v;
+    };
+    const float n = G(x - 1, y), s = G(x + 1, y), w = G(x, y - 1), e = G(x, y + 1), nw = G(x - 1, y - 1),
+                ne = G(x - 1, y + 1), sw = G(x + 1, y - 1), se = G(x + 1, y + 1);
+    const float tl = C(x - 1, y - 1), tr = C(x - 1, y), bl = C(x, y - 1), br = C(x, y);
+    const float g1[8] = {n, n, w, w, s, s, e, e}, g2[8] = {ne, nw, nw, sw, sw, se, se, ne};
+    const float b[8] = {tl, tr, bl, tl, br, bl, tr, br}, c[8] = {tr, tl, tl, bl, bl, br, br, tr};
+    for (int k = 0; k < 8; ++k)
+        out[k] = kind == TASI_KIND_FD ? tasi::fd_tri(g1[k], g2[k], b[k], c[k]) : tasi::mfd_tri(g1[k], g2[k], c[k]);
 }
 }

@@ -290,6 +290,13 @@ class GpuReplanner {
         check(tasi_read_field(h_, f.data()), "tasi_read_field");
         return f;
     }
+    // INFO of the reference's level-1 planners, on demand: 4 signed bytes per element of the window, the offsets of
+    // its two parents ((0, 0) = absent); FD*/MFD*: b and ccw(b), MS-DFM: the lower and the higher stencil cell
+    std::vector<signed char> read_parents(int x0, int y0, int nx, int ny) const {
+        std::vector<signed char> out((size_t) nx * ny * 4);
+        check(tasi_read_parents(h_, x0, y0, nx, ny, out.data()), "tasi_read_parents");
+        return out;
+    }
     // half-side of the window exported to the reference's ExpandedMap after a step (reference-types mode);
     // the extractor walks at most max_steps cells from the start (default 20), <= 0 exports the whole field
     int handoff_radius = 48;

@@ -226,6 +226,16 @@ class GpuPlanner:
         self._check(self._L.tasi_band_delta(self._h, C.byref(d)))
         return d.value
 
+    def read_parents(self, x0=0, y0=0, nx=None, ny=None):
+        """Parent (back-pointer) field of the window: (nx, ny, 4) int8 offsets (dx1, dy1, dx2, dy2) of the two parents of
+        every element, (0, 0) = absent — what the reference's level-1 planners keep as INFO (tasi_read_parents)."""
+        ex, ey = self.field_dims()
+        nx = ex - x0 if nx is None else nx
+        ny = ey - y0 if ny is None else ny
+        out = np.zeros((nx, ny, 4), np.int8)
+        self._check(self._L.tasi_read_parents(self._h, x0, y0, nx, ny, out.ctypes.data_as(C.c_void_p)))
+        return out
+
     def set_focus(self, enabled=True, slack=-1.0):
         """Plans stop once the start is settled (the reference's end_condition); later work stays parked and is
         resumed by the next step(). slack < 0 = default."""

@@ -166,6 +166,14 @@ int tasi_band_solve_until(tasi_planner *p, float limit, uint64_t *n_tile_visits,
 /* Width of the value band one threshold advance covers on this band's map (delta_factor * 32 * mean free cost). */
 int tasi_band_delta(tasi_planner *p, float *delta);
 
+/* A stack of n_blocks independent maps of `length` rows each in one planner, one obstacle row (255) between
+ * consecutive blocks: the layout tasi_set_goals (one goal per block) and tasi_extract_paths' row_ranges work on
+ * (block b = cell rows b * (length + 1) ... + length - 1). Block b shows maps[index[b]]; every distinct map crosses
+ * the bus once and is replicated on the device. Host pointers are not retained. Batches of queries
+ * (BASELINE.json cfg5); the reference plans one query at a time (set_map + set_goal + step per query). */
+int tasi_set_map_stack(tasi_planner *p, const uint8_t *const *maps, int n_maps, const int *index, int n_blocks,
+                       int width, int length);
+
 /* ---- focused planning ----
  * The reference's plan() stops once the start is settled (end_condition: FieldDPlanner_impl.h:225-256 waits for the
  * four corner nodes of the start cell, DynamicFastMarching_impl.h:315-320 for the start cell; the shifted-grid

@@ -76,6 +76,7 @@ SIGNATURES = {
     "tasi_band_solve_until": (C.c_int, [C.c_void_p, C.c_float, _u64p, _f32p]),
     "tasi_band_delta": (C.c_int, [C.c_void_p, _f32p]),
     "tasi_read_parents": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),
+    "tasi_set_map_stack": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.c_int, _i32p, C.c_int, C.c_int, C.c_int]),
     "tasi_set_focus": (C.c_int, [C.c_void_p, C.c_int, C.c_float]),
     "tasi_extract_paths": (C.c_int, [C.c_void_p, _f32p, _f32p, _i32p, C.c_int, C.c_int, C.c_int, C.c_int, _f32p, C.c_int,
                                      _i32p, _f32p, C.c_int, _i32p, _f32p, _i32p, _f32p]),

@@ -85,7 +85,13 @@ class StackedBatch:
         self.L, self.W = maps[0].shape
         self.n = len(maps)
         self.p.set_occupancy_threshold(occ)
-        self.p.set_map(stack_maps(maps))
+        distinct, index, seen = [], [], {}
+        for m in maps:  # the same array object asked several times crosses the bus once
+            if id(m) not in seen:
+                seen[id(m)] = len(distinct)
+                distinct.append(m)
+            index.append(seen[id(m)])
+        self.p.set_map_stack(distinct, index)
         off = self.L + 1
         self.p.set_start(0.0, 0.0)
         self.goals = [tuple(g) for g in goals]

@@ -420,6 +420,38 @@ int tasi_set_map_device(tasi_planner *p, const uint8_t *dev_map, int width, int 
     return set_map_common(p, dev_map, width, length, pitch, cudaMemcpyDeviceToDevice);
 }
 
+int tasi_set_map_stack(tasi_planner *p, const uint8_t *const *maps, int n_maps, const int *index, int n_blocks,
+                       int width, int length) {
+    if (!p || !maps || !index || n_maps <= 0 || n_blocks <= 0 || width <= 0 || length <= 0) return TASI_ERR_ARG;
+    if (p->open_top || p->open_bottom) return fail(p, TASI_ERR_STATE, "set_map_stack: not available on a row band");
+    for (int b = 0; b < n_blocks; ++b)
+        if (index[b] < 0 || index[b] >= n_maps || !maps[index[b]]) return fail(p, TASI_ERR_ARG, "set_map_stack: bad index");
+    CU_TRY(p, cudaSetDevice(p->device));
+    const int64_t rows = (int64_t) n_blocks * (length + 1) - 1;
+    if (rows > INT32_MAX) return fail(p, TASI_ERR_ARG, "set_map_stack: too many rows");
+    int rc = alloc_grid(p, width, (int) rows);
+    if (rc != TASI_OK) return rc;
+    // every distinct map crosses the bus once (into the first block that shows it); its other blocks are device copies
+    std::vector<int> first(n_maps, -1);
+    for (int b = 0; b < n_blocks; ++b) {
+        uint8_t *dst = c_origin(p) + (int64_t) b * (length + 1) * p->cpitch;
+        const int m = index[b];
+        if (first[m] < 0) {
+            first[m] = b;
+            CU_TRY(p, cudaMemcpy2DAsync(dst, p->cpitch, maps[m], width, width, length, cudaMemcpyHostToDevice, p->stream));
+        } else {
+            const uint8_t *src = c_origin(p) + (int64_t) first[m] * (length + 1) * p->cpitch;
+            CU_TRY(p, cudaMemcpy2DAsync(dst, p->cpitch, src, p->cpitch, width, length, cudaMemcpyDeviceToDevice, p->stream));
+        }
+        if (b + 1 < n_blocks)  // the obstacle row that keeps the blocks apart
+            CU_TRY(p, cudaMemset2DAsync(dst + (int64_t) length * p->cpitch, p->cpitch, 255, width, 1, p->stream));
+    }
+    CU_TRY(p, cudaStreamSynchronize(p->stream));  // host pointers are not retained
+    p->initialize_graph = false;
+    p->cost_stats_valid = false;
+    return TASI_OK;
+}
+
 int tasi_synth_map(tasi_planner *p, uint64_t seed, int width, int length, int64_t row0, int p_obs, int sx, int sy,
                    int gx, int gy) {
     if (!p || width <= 0 || length <= 0) return TASI_ERR_ARG;

@@ -226,6 +226,18 @@ class GpuPlanner:
         self._check(self._L.tasi_band_delta(self._h, C.byref(d)))
         return d.value
 
+    def set_map_stack(self, maps, index):
+        """A stack of independent maps (equal shapes), block b showing maps[index[b]], an obstacle row between blocks
+        (tasi_set_map_stack): each distinct map is uploaded once and replicated on the device."""
+        arrs = [np.ascontiguousarray(m, np.uint8) for m in maps]
+        L, W = arrs[0].shape
+        assert all(a.shape == (L, W) for a in arrs)
+        ptrs = (C.c_void_p * len(arrs))(*[a.ctypes.data for a in arrs])
+        idx = np.ascontiguousarray(index, np.int32)
+        self.length, self.width = len(idx) * (L + 1) - 1, W
+        self._check(self._L.tasi_set_map_stack(self._h, ptrs, len(arrs), idx.ctypes.data_as(C.POINTER(C.c_int32)),
+                                               len(idx), W, L))
+
     def read_parents(self, x0=0, y0=0, nx=None, ny=None):
         """Parent (back-pointer) field of the window: (nx, ny, 4) int8 offsets (dx1, dy1, dx2, dy2) of the two parents of
         every element, (0, 0) = absent — what the reference's level-1 planners keep as INFO (tasi_read_parents)."""

@@ -7,8 +7,8 @@
 // through that edge and the points the path gains. Float32 in the reference's operation order, no FMA
 // contraction (nvcc -fmad=false, gcc -ffp-contract=off); hypotf as glibc computes it (in double).
 //
-// One candidate edge = one call of hop_over_edge(); the device kernel (tasi_extract_kernel.cuh) gives each lane
-// of a warp one candidate, the host build (tasi_hostops.cpp, tests only) loops.
+// One candidate edge = one call of hop_over_edge(); the device kernel at the end of this file gives each lane of a
+// warp one candidate, the host build (tasi_hostops.cpp, tests only) loops.
 #pragma once
 #include "tasi_update.cuh"
 

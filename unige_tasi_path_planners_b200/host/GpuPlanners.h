@@ -14,6 +14,10 @@
 // get_grid, and the public data u_time, p_time, num_nodes_updated, num_nodes_expanded, heuristic_multiplier,
 // the five state flags, grid and map.
 //
+//   tasi_host::GpuPathExtractor<Planner>   stands in for LinearInterpolationPathExtractor<E,T>
+//                                          (PathExtraction/LinearInterpolationPathExtractor.h:9-22), walk on the device
+// Beyond the reference: set_focus (its end_condition as a switch), read_parents (its level-1 INFO on demand), stats.
+//
 // Two build modes:
 //   * default (stand-alone): Position / Node / Cell / HostGrid / FieldMap below are this repo's own small types
 //     with the reference's member names; FieldMap is a dense view of the device field that fetches windows on
@@ -355,8 +359,7 @@ class GpuReplanner {
 // LinearInterpolationPathExtractor (PathExtraction/LinearInterpolationPathExtractor.h:9-22) with the walk on the
 // device: same public members; bound to the planner instead of to its (map, grid) pair, because the field never
 // leaves the GPU. One extract_path() = one launch of the warp-per-walk kernel (tasi_extract_paths) and one D2H of
-// the positions;
-// the hand-off window of reference-types mode is not read on this route.
+// the positions; the hand-off window of reference-types mode is not read on this route.
 template <typename Planner>
 class GpuPathExtractor {
  public:

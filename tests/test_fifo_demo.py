@@ -139,7 +139,8 @@ def test_fifo_drive_to_the_goal(exe, oracle, kind, focus, tmp_path):
     indirect = kind != "mfd"              # SGDFM/main.cpp:97
     for i, (pos, kmap, path, costs, totals, times, recs, _) in enumerate(steps):
         p0 = (pos[0] - off, pos[1] - off)
-        assert tuple(path[0]) == p0
+        assert np.allclose(path[0], p0, atol=1e-5, rtol=0)  # (the float32 "+ 0.5" of the DFM report is not exactly undone)
+        p0 = (float(path[0][0]), float(path[0][1]))
         want = oracle.solve(k, kmap, goal)
         hw = _lib.host_extract(k == 1, want, kmap, p0, goal, 255, 20, True, indirect)
         if k != 1:

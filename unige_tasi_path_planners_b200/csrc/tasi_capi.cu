@@ -54,7 +54,8 @@ struct tasi_planner {
     unsigned long long *cost_sum = nullptr;  // device: {sum of free-cell costs, number of free cells}
     bool cost_stats_valid = false;
     float mean_cost = 1.0f;
-    float delta_factor = 2.0f;
+    float delta_factor = 2.0f;  // width of the value band per threshold advance, in tiles of mean cost
+    bool delta_auto = true;     // ... widened on small grids (band_width()), unless TASI_DELTA_FACTOR fixes it
     DevCtl *ctl = nullptr;
     float *stage = nullptr;  // 2 x EY receive rows (band mode)
     uint8_t *patch_buf = nullptr, *chg_buf = nullptr;
@@ -99,6 +100,20 @@ inline int fail(tasi_planner *p, int code, const char *what) {
 
 inline bool node_based(const tasi_planner *p) { return p->kind != TASI_DFM; }
 
+// Value width of one threshold advance. A wider band releases more tiles at once (more CTAs busy) and re-runs
+// more of them; measured (scripts/sweep_delta.sh, all three planners): the best factor is 2 from 16384^2 up, 3 at
+// 8192^2 / 4096^2, 6-8 at 2048^2 / 1024^2, within a 15 % spread — small grids have too short a front to feed the
+// CTAs otherwise. Row bands keep the plain factor (their threshold is shared across ranks), and so do focused plans
+// (the band is the granularity at which they can stop).
+inline float band_width(const tasi_planner *p) {
+    float f = p->delta_factor;
+    if (p->delta_auto && f > 0.0f && !p->focus && !p->open_top && !p->open_bottom) {
+        const double nt = std::max(1.0, (double) p->TX * (double) p->TY);
+        f = (float) std::min(6.0, std::max(2.0, 2.0 + 0.5 * std::log2(262144.0 / nt)));
+    }
+    return f * (float) TS * p->mean_cost;
+}
+
 inline float *g_origin(const tasi_planner *p) { return p->g_base + p->gpitch + GMARGIN; }
 inline uint8_t *c_origin(const tasi_planner *p) { return p->c_base + p->cpitch + GMARGIN; }
 
@@ -119,7 +134,7 @@ GridDesc make_desc(const tasi_planner *p) {
     d.state = p->state; d.queue = p->queue; d.qmask = p->qsize - 1;
     d.seed = p->seed; d.ctl = p->ctl;
     d.key = p->key; d.far = p->far; d.far_cap = p->far_cap;
-    d.delta = p->delta_factor * (float) TS * p->mean_cost;
+    d.delta = band_width(p);
     d.inval_tol = (p->kind == TASI_DFM) ? 1e-6f : 0.0f;
     d.n_focus = 0;
     d.focus_slack = p->focus_slack;
@@ -358,7 +373,10 @@ int tasi_create(int kind, int level, int device, tasi_planner **out) {
         double v = atof(e);
         if (v > 0) p->timeout_s = v;
     }
-    if (const char *e = getenv("TASI_DELTA_FACTOR")) p->delta_factor = (float) atof(e);  // <= 0: no ordering
+    if (const char *e = getenv("TASI_DELTA_FACTOR")) {  // fixed factor; <= 0: no ordering
+        p->delta_factor = (float) atof(e);
+        p->delta_auto = false;
+    }
     *out = p;
     return TASI_OK;
 }
@@ -769,7 +787,7 @@ int tasi_band_delta(tasi_planner *p, float *delta) {
     CU_TRY(p, cudaSetDevice(p->device));
     int rc = ensure_cost_stats(p);
     if (rc != TASI_OK) return rc;
-    *delta = p->delta_factor * (float) TS * p->mean_cost;
+    *delta = band_width(p);
     return TASI_OK;
 }
 

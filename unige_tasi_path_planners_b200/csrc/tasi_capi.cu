@@ -70,6 +70,7 @@ struct tasi_planner {
     uint64_t last_seed_count = 0;
 
     int solver_blocks = 0, max_blocks = 0;
+    int strip = 4;  // elements per thread of a tile row in the solver instance this grid uses (alloc_grid)
     // focused planning (tasi_set_focus): plans stop once the start is settled, the rest stays parked
     bool focus = false;
     float focus_slack = 4.0f * 254.0f;
@@ -160,15 +161,20 @@ void free_grid(tasi_planner *p) {
 }
 
 typedef void (*solver_fn)(GridDesc);
-solver_fn pick_solver(int kind, int mode) {
+template <int SW>
+solver_fn pick_solver_sw(int kind, int mode) {
     switch (kind * 2 + mode) {
-        case TASI_FD * 2 + 0: return solver_kernel<TASI_KIND_FD, 0>;
-        case TASI_FD * 2 + 1: return solver_kernel<TASI_KIND_FD, 1>;
-        case TASI_DFM * 2 + 0: return solver_kernel<TASI_KIND_DFM, 0>;
-        case TASI_DFM * 2 + 1: return solver_kernel<TASI_KIND_DFM, 1>;
-        case TASI_MFD * 2 + 0: return solver_kernel<TASI_KIND_MFD, 0>;
-        default: return solver_kernel<TASI_KIND_MFD, 1>;
+        case TASI_FD * 2 + 0: return solver_kernel<TASI_KIND_FD, 0, SW>;
+        case TASI_FD * 2 + 1: return solver_kernel<TASI_KIND_FD, 1, SW>;
+        case TASI_DFM * 2 + 0: return solver_kernel<TASI_KIND_DFM, 0, SW>;
+        case TASI_DFM * 2 + 1: return solver_kernel<TASI_KIND_DFM, 1, SW>;
+        case TASI_MFD * 2 + 0: return solver_kernel<TASI_KIND_MFD, 0, SW>;
+        default: return solver_kernel<TASI_KIND_MFD, 1, SW>;
     }
+}
+// strip = elements per thread of a tile row: 4 (256-thread CTAs, two per SM) or 2 (512-thread CTAs, one per SM)
+solver_fn pick_solver(int kind, int mode, int strip) {
+    return strip == 2 ? pick_solver_sw<2>(kind, mode) : pick_solver_sw<4>(kind, mode);
 }
 
 // (Re)allocate the device arrays for a map of `rows` x `W` cells. Margins: cost bytes 255, values INF.
@@ -187,15 +193,23 @@ int alloc_grid(tasi_planner *p, int W, int rows) {
     p->g_rows = (int64_t) p->TX * TS + 2;
     const int nt = p->TX * p->TY;
     int dev_blocks = 0;
-    CU_TRY(p, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&dev_blocks, pick_solver(p->kind, 0), NTHREADS, 0));
+    // A relaxation round is issue- and latency-bound inside its SM, and a mid-size grid's front never offers more
+    // active tiles than SMs x a few. There ONE CTA per SM with 512 threads and 2-element strips halves the serial
+    // work of a thread per round and beats two 256-thread CTAs per SM; from some grid size on the second CTA's
+    // extra tile in flight wins. Measured cross-over (tiles), per operator weight (scripts/quick_bench.py with
+    // TASI_STRIP=2|4; FD* 4096^2 34.1 -> 30.0 ms, 8192^2 97 -> 86 ms; MFD* 4096^2 21.5 -> 18.0 ms; MS-DFM 2048^2 8.4 -> 8.1):
+    const int strip2_upto = p->kind == TASI_FD ? 100000 : (p->kind == TASI_MFD ? 70000 : 4200);
+    p->strip = nt <= strip2_upto ? 2 : 4;
+    if (const char *e = getenv("TASI_STRIP")) {
+        const int v = atoi(e);
+        if (v == 2 || v == 4) p->strip = v;
+    }
+    const int nthreads = TS * TS / p->strip;
+    CU_TRY(p, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&dev_blocks, pick_solver(p->kind, 0, p->strip), nthreads, 0));
     int dev_blocks1 = 0;
-    CU_TRY(p, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&dev_blocks1, pick_solver(p->kind, 1), NTHREADS, 0));
+    CU_TRY(p, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&dev_blocks1, pick_solver(p->kind, 1, p->strip), nthreads, 0));
     if (dev_blocks1 < dev_blocks) dev_blocks = dev_blocks1;
     if (dev_blocks < 1) { p->err = "solver kernel does not fit on an SM"; return TASI_ERR_CUDA; }
-    // A relaxation round is issue-bound inside its SM, so a CTA alone on an SM turns rounds over ~25 % faster
-    // than two sharing one; grids up to ~4096^2 never have more active tiles than SMs x a few, so the node
-    // planners (the heavier operators) run one CTA per SM there and two above (measured: FD* 4096^2 42 -> 36 ms).
-    if (node_based(p) && nt <= 32768 && dev_blocks > 1) dev_blocks = 1;
     int blocks = dev_blocks * p->num_sms;
     if (const char *e = getenv("TASI_BLOCKS_PER_SM")) {
         int v = atoi(e);
@@ -281,7 +295,7 @@ int run_solver(tasi_planner *p, int mode, float *ms, bool resume = false, float 
     enqueue_seeds_kernel<<<std::min((nt + 255) / 256, 1024), 256, 0, p->stream>>>(d, ordered);
     arm_solver_kernel<<<1, 1, 0, p->stream>>>(d);
     const int nblocks = (p->max_blocks > 0 && p->max_blocks < p->solver_blocks) ? p->max_blocks : p->solver_blocks;
-    pick_solver(p->kind, mode)<<<nblocks, NTHREADS, 0, p->stream>>>(d);
+    pick_solver(p->kind, mode, p->strip)<<<nblocks, TS * TS / p->strip, 0, p->stream>>>(d);
     CU_TRY(p, cudaGetLastError());
     CU_TRY(p, cudaEventRecord(p->ev1, p->stream));
     DevCtl h;

@@ -189,11 +189,12 @@ __device__ inline void activate(const GridDesc &d, int tile, int kbits, int dirb
 // the pile stays as it is and the launch ends (band mode: the host exchanges halos and raises the limit).
 __device__ inline bool advance_threshold(const GridDesc &d, int *s_red, int tid) {
     DevCtl *c = d.ctl;
+    const int nthreads = blockDim.x;  // 256 or 512 (the strip width of the kernel instance)
     const int cur = *(volatile int *) &c->far_sel;
     const int n = min(*(volatile int *) &c->far_count[cur], d.far_cap);
     const int *src = d.far + cur * d.far_cap;
     int m = INF_BITS;
-    for (int i = tid; i < n; i += NTHREADS) {
+    for (int i = tid; i < n; i += nthreads) {
         const int t = __ldcg(src + i);
         if (*(volatile int *) &d.state[t] & ST_FAR) m = min(m, *(volatile int *) &d.key[t]);
     }
@@ -201,8 +202,7 @@ __device__ inline bool advance_threshold(const GridDesc &d, int *s_red, int tid)
     if ((tid & 31) == 0) s_red[tid >> 5] = m;
     __syncthreads();
     m = s_red[0];
-#pragma unroll
-    for (int w = 1; w < NTHREADS / 32; ++w) m = min(m, s_red[w]);
+    for (int w = 1; w < nthreads / 32; ++w) m = min(m, s_red[w]);
     const int lim = *(volatile int *) &c->limit_bits;
     if (tid == 0) c->far_min_bits = m;
     if (m != INF_BITS && m >= lim) return true;
@@ -235,7 +235,7 @@ __device__ inline bool advance_threshold(const GridDesc &d, int *s_red, int tid)
     }
     __syncthreads();
     int *dst = d.far + (cur ^ 1) * d.far_cap;
-    for (int i = tid; i < n; i += NTHREADS) {
+    for (int i = tid; i < n; i += nthreads) {
         const int t = __ldcg(src + i);
         if (!(*(volatile int *) &d.state[t] & ST_FAR)) continue;  // stale entry (tile was promoted)
         if (*(volatile int *) &d.key[t] < nthr || nthr == INF_BITS) {
@@ -295,11 +295,11 @@ __device__ inline void drain_and_advance(const GridDesc &d, int *s_red, int *s_a
 // Direction bits: which halo side of a tile changed (set by the neighbour that wrote it); they select the
 // strips that evaluate in the first round (the others only take their copy).
 constexpr int IN_N = 1, IN_S = 2, IN_W = 4, IN_E = 8, IN_NW = 16, IN_NE = 32, IN_SW = 64, IN_SE = 128, IN_ALL = 256;
-constexpr int SW = 4;             // strip width
-constexpr int WIN_R = 3, WIN_C = SW + 2;
+constexpr int WIN_R = 3;          // a strip of SW elements reads a 3 x (SW + 2) window
+constexpr int MAX_WARPS = 16;     // per CTA, over the kernel instances (SW = 2: 512 threads)
 
-template <int KIND>
-__device__ __forceinline__ float eval_strip_elem(const float (&w)[WIN_R][WIN_C], const float (&cw)[2][SW + 1], int j) {
+template <int KIND, int SW>
+__device__ __forceinline__ float eval_strip_elem(const float (&w)[WIN_R][SW + 2], const float (&cw)[2][SW + 1], int j) {
     Nbr8 nb;
     nb.n = w[0][j + 1]; nb.s = w[2][j + 1]; nb.w = w[1][j]; nb.e = w[1][j + 2];
     nb.nw = w[0][j]; nb.ne = w[0][j + 2]; nb.sw = w[2][j]; nb.se = w[2][j + 2];
@@ -311,11 +311,12 @@ __device__ __forceinline__ float eval_strip_elem(const float (&w)[WIN_R][WIN_C],
 
 // Relax (MODE 0) or invalidate (MODE 1) the staged tile to local convergence. w[1][1..4] holds the strip's final
 // values on return; chg gets one bit per strip element that changed during the visit.
-template <int KIND, int MODE>
+template <int KIND, int MODE, int SW>
 __device__ __forceinline__ int relax_tile(float *sg, const float *sc, int inmask, int row, int col0, int rlim, int clim,
-                                          int pin_r, int pin_c, float tol, float (&w)[WIN_R][WIN_C],
+                                          int pin_r, int pin_c, float tol, float (&w)[WIN_R][SW + 2],
                                           unsigned &chg, unsigned &iters, unsigned &evals) {
     const float INF = __int_as_float(0x7f800000);
+    constexpr int WIN_C = SW + 2;
     // which strip elements exist and may be written (the goal element is pinned, FieldDPlanner_impl.h:47,146)
     unsigned live = 0;
 #pragma unroll
@@ -358,7 +359,7 @@ __device__ __forceinline__ int relax_tile(float *sg, const float *sc, int inmask
         if (dirty && live) {
             float v[SW];
 #pragma unroll
-            for (int j = 0; j < SW; ++j) v[j] = eval_strip_elem<KIND>(w, cw, j);
+            for (int j = 0; j < SW; ++j) v[j] = eval_strip_elem<KIND, SW>(w, cw, j);
 #pragma unroll
             for (int j = 0; j < SW; ++j) {
                 const float cur = w[1][j + 1];
@@ -389,21 +390,23 @@ __device__ __forceinline__ int relax_tile(float *sg, const float *sc, int inmask
 // L2 round trip.
 constexpr int GV_PER_ROW = 10;
 constexpr int G_VECS = (TS + 2) * GV_PER_ROW;                                  // 340 float4 per tile
-constexpr int G_ITERS = (G_VECS + NTHREADS - 1) / NTHREADS;                    // 3
 constexpr int C_ROWS_NODE = TS + 1, C_ROWS_CELL = TS;
-constexpr int C_ITERS = (C_ROWS_NODE * GV_PER_ROW + NTHREADS - 1) / NTHREADS;  // 3
 
-template <int KIND, int MODE>
-__global__ void __launch_bounds__(NTHREADS, 2) solver_kernel(GridDesc d) {
+// SW = strip width: 4 (256 threads, two CTAs per SM) or 2 (512 threads, one CTA per SM: half the serial work per
+// thread in a round, for the node planners on grids whose front never feeds more than one CTA per SM anyway).
+template <int KIND, int MODE, int SW>
+__global__ void __launch_bounds__(1024 / SW, SW == 4 ? 2 : 1) solver_kernel(GridDesc d) {
+    constexpr int NT = (TS * TS) / SW, WIN_C = SW + 2;
+    constexpr int G_ITERS = (G_VECS + NT - 1) / NT, C_ITERS = (C_ROWS_NODE * GV_PER_ROW + NT - 1) / NT;
     __shared__ float sg[(TS + 2) * GP];   // values, rows/cols -1..32
     __shared__ float sc[(TS + 1) * CP];   // cell costs as float, INF = obstacle
     __shared__ int s_tile, s_inmask, s_again, s_adv;
     __shared__ int s_kmin[8];             // per neighbour direction: lowest changed value it will read (bits)
-    __shared__ int s_red[NTHREADS / 32];
+    __shared__ int s_red[MAX_WARPS];
 
     const float INF = __int_as_float(0x7f800000);
     const int tid = threadIdx.x, lane = tid & 31;
-    const int row = tid >> 3, col0 = (tid & 7) * SW;  // this thread's strip
+    const int row = tid / (TS / SW), col0 = (tid % (TS / SW)) * SW;  // this thread's strip
     unsigned long long n_visits = 0, n_iters = 0, n_changed = 0, n_evals = 0;
     long long c_pop = 0, c_stage = 0, c_relax = 0, c_post = 0, c0 = clock64(), c1;
 
@@ -450,7 +453,7 @@ __global__ void __launch_bounds__(NTHREADS, 2) solver_kernel(GridDesc d) {
         uchar4 cv[C_ITERS];
 #pragma unroll
         for (int k = 0; k < C_ITERS; ++k) {
-            const int i = tid + k * NTHREADS;
+            const int i = tid + k * NT;
             const int r = i / GV_PER_ROW, v = i - r * GV_PER_ROW;
             if (i < c_rows * GV_PER_ROW)
                 cv[k] = __ldg((const uchar4 *) (d.cost + (int64_t) (x0 + c_r0 + r) * d.cpitch + (y0 - 4 + 4 * v)));
@@ -463,7 +466,7 @@ __global__ void __launch_bounds__(NTHREADS, 2) solver_kernel(GridDesc d) {
             float4 gv[G_ITERS];
 #pragma unroll
             for (int k = 0; k < G_ITERS; ++k) {
-                const int i = tid + k * NTHREADS;
+                const int i = tid + k * NT;
                 const int r = i / GV_PER_ROW, v = i - r * GV_PER_ROW;
                 if (i < G_VECS)
                     gv[k] = __ldcg((const float4 *) (d.g + (int64_t) (x0 - 1 + r) * d.gpitch + (y0 - 4 + 4 * v)));
@@ -472,7 +475,7 @@ __global__ void __launch_bounds__(NTHREADS, 2) solver_kernel(GridDesc d) {
                 first = false;
 #pragma unroll
                 for (int k = 0; k < C_ITERS; ++k) {
-                    const int i = tid + k * NTHREADS;
+                    const int i = tid + k * NT;
                     const int r = i / GV_PER_ROW, v = i - r * GV_PER_ROW;
                     if (i < c_rows * GV_PER_ROW) {
                         const unsigned char bb[4] = {cv[k].x, cv[k].y, cv[k].z, cv[k].w};
@@ -486,7 +489,7 @@ __global__ void __launch_bounds__(NTHREADS, 2) solver_kernel(GridDesc d) {
             }
 #pragma unroll
             for (int k = 0; k < G_ITERS; ++k) {
-                const int i = tid + k * NTHREADS;
+                const int i = tid + k * NT;
                 const int r = i / GV_PER_ROW, v = i - r * GV_PER_ROW;
                 if (i < G_VECS) {
                     const float ff[4] = {gv[k].x, gv[k].y, gv[k].z, gv[k].w};
@@ -507,7 +510,7 @@ __global__ void __launch_bounds__(NTHREADS, 2) solver_kernel(GridDesc d) {
             for (int a2 = 0; a2 < WIN_R; ++a2)
 #pragma unroll
                 for (int b2 = 0; b2 < WIN_C; ++b2) w[a2][b2] = 0.0f;
-            n_changed += relax_tile<KIND, MODE>(sg, sc, s_inmask, row, col0, rlim, clim, pin_r, pin_c, d.inval_tol, w, chg,
+            n_changed += relax_tile<KIND, MODE, SW>(sg, sc, s_inmask, row, col0, rlim, clim, pin_r, pin_c, d.inval_tol, w, chg,
                                                 it, ev);
             n_iters += it;   // counted once per CTA below (every thread sees the same number of rounds)
             n_evals += ev;
@@ -517,8 +520,8 @@ __global__ void __launch_bounds__(NTHREADS, 2) solver_kernel(GridDesc d) {
             // it reads
             if (chg) {
                 float *gp = d.g + (int64_t) (x0 + row) * d.gpitch + (y0 + col0);
-                if (chg == 0xfu) {
-                    *(float4 *) gp = make_float4(w[1][1], w[1][2], w[1][3], w[1][4]);
+                if (SW == 4 && chg == 0xfu) {
+                    *(float4 *) gp = make_float4(w[1][1], w[1][2], w[1][3], w[1][SW]);
                 } else {
 #pragma unroll
                     for (int j = 0; j < SW; ++j)

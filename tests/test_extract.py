@@ -200,3 +200,34 @@ def test_gpu_walk_argument_errors():
     res, _ = p.extract_paths([(2.0, 2.0)], [(12.0, 12.0)], 100, cap_points=3)
     assert res[0]["status"] == 3
     p.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("kind", [0, 2])
+def test_gpu_full_size_walk_descends_to_the_goal(kind):
+    """BASELINE.json's 4096 x 4096 grid: no oracle at this size, but a walk has size-independent properties — it ends
+    on the goal, the field never rises along its vertices, and its cost re-integrates the field value at the start."""
+    from unige_tasi_path_planners_b200 import PLANNERS
+    N = 4096
+    start, goal = synth.default_endpoints(N, N)
+    p = PLANNERS[kind](1)
+    p.set_occupancy_threshold(1.0)
+    p.synth_map(1, N, N, 0, 10, start, goal)
+    p.set_start(*start)
+    p.set_goal(*goal)
+    assert p.step() == 0
+    res, ms = p.extract_paths(None, None, 40000, cap_points=120001)
+    w = res[0]
+    assert w["status"] == 0 and tuple(w["path"][-1]) == goal and tuple(w["path"][0]) == start
+    assert len(w["path"]) > N  # at least one point per row crossed
+    g0 = float(p.read_window(int(start[0]), int(start[1]), 1, 1)[0, 0])
+    assert w["total_cost"] == pytest.approx(g0, rel=2e-2)
+    assert w["total_dist"] >= np.hypot(goal[0] - start[0], goal[1] - start[1]) * 0.999
+    # field values at the path's vertices (positions with integer coordinates) never rise
+    pts = w["path"]
+    vert = (pts == np.floor(pts)).all(axis=1)
+    vs = pts[vert].astype(np.int64)
+    step = max(1, len(vs) // 400)
+    vals = [float(p.read_window(int(x), int(y), 1, 1)[0, 0]) for x, y in vs[::step]]
+    assert all(b <= a for a, b in zip(vals, vals[1:]))
+    p.close()

@@ -26,6 +26,10 @@ import sys
 import threading
 import time
 
+# rank 0 prints ONE JSON line on stdout: NCCL's version banner (NCCL_DEBUG=VERSION, set on some boxes) goes there too
+if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+    os.environ["NCCL_DEBUG"] = "WARN"
+
 ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)

@@ -342,7 +342,7 @@ __device__ __forceinline__ int relax_tile(float *sg, const float *sc, int inmask
     const float *base = sg + row * GP + col0;  // window origin: element (row-1, col0-1)
     int cnt_changed = 0;
     chg = 0;
-    bool firstround = true;
+    bool firstround = true, self_changed = false;
     for (;;) {
         bool diff = false;
 #pragma unroll
@@ -353,26 +353,59 @@ __device__ __forceinline__ int relax_tile(float *sg, const float *sc, int inmask
                 diff |= __float_as_int(x) != __float_as_int(w[a][b]);
                 w[a][b] = x;
             }
-        if (!firstround) dirty = diff;
+        if (!firstround) dirty = diff || self_changed;
         firstround = false;
+        self_changed = false;
         bool stored = false;
         if (dirty && live) {
-            float v[SW];
+            if (MODE == 0 && SW == 4 && KIND != TASI_KIND_DFM) {
+                // Gauss-Seidel along the strip, direction alternating from round to round: an element reads the value its
+                // strip-mate just took, so a change crosses the whole strip in one round instead of one element
+                // (node planners with 4-element strips: 15.4 -> 13.7 rounds per visit, MFD* 16384^2 154 -> 134 ms;
+                // measured slower for 2-element strips and for MS-DFM, which keep the Jacobi order below)
+                if (iters & 1u) {
 #pragma unroll
-            for (int j = 0; j < SW; ++j) v[j] = eval_strip_elem<KIND, SW>(w, cw, j);
+                    for (int j = SW - 1; j >= 0; --j) {
+                        const float v = eval_strip_elem<KIND, SW>(w, cw, j);
+                        if (v < w[1][j + 1] && ((live >> j) & 1u)) {
+                            w[1][j + 1] = v;
+                            sg[(row + 1) * GP + col0 + 1 + j] = v;
+                            chg |= 1u << j;
+                            ++cnt_changed;
+                            stored = true;
+                        }
+                    }
+                } else {
 #pragma unroll
-            for (int j = 0; j < SW; ++j) {
-                const float cur = w[1][j + 1];
-                bool c;
-                if (MODE == 0) c = v[j] < cur;
-                else c = cur < INF && cur > 0.0f && v[j] > cur + cur * tol;  // 0 = a goal (costs are >= 1): pinned
-                c = c && ((live >> j) & 1u);
-                if (c) {
-                    const float nv = (MODE == 0) ? v[j] : INF;
-                    sg[(row + 1) * GP + col0 + 1 + j] = nv;
-                    chg |= 1u << j;
-                    ++cnt_changed;
-                    stored = true;
+                    for (int j = 0; j < SW; ++j) {
+                        const float v = eval_strip_elem<KIND, SW>(w, cw, j);
+                        if (v < w[1][j + 1] && ((live >> j) & 1u)) {
+                            w[1][j + 1] = v;
+                            sg[(row + 1) * GP + col0 + 1 + j] = v;
+                            chg |= 1u << j;
+                            ++cnt_changed;
+                            stored = true;
+                        }
+                    }
+                }
+                self_changed = stored;
+            } else {
+                float v[SW];
+#pragma unroll
+                for (int j = 0; j < SW; ++j) v[j] = eval_strip_elem<KIND, SW>(w, cw, j);
+#pragma unroll
+                for (int j = 0; j < SW; ++j) {
+                    const float cur = w[1][j + 1];
+                    bool c;
+                    if (MODE == 0) c = v[j] < cur;
+                    else c = cur < INF && cur > 0.0f && v[j] > cur + cur * tol;  // 0 = a goal (costs are >= 1): pinned
+                    c = c && ((live >> j) & 1u);
+                    if (c) {
+                        sg[(row + 1) * GP + col0 + 1 + j] = (MODE == 0) ? v[j] : INF;
+                        chg |= 1u << j;
+                        ++cnt_changed;
+                        stored = true;
+                    }
                 }
             }
             evals += SW;

@@ -272,3 +272,69 @@ def test_full_size_cfg2_field_is_a_fixed_point(oracle, kind):
         reach = lab == lab[int(goal[0]), int(goal[1])]
         assert np.array_equal(np.isfinite(got), reach)
     assert np.isfinite(got[int(start[0]), int(start[1])])
+
+
+def compare_settled(kind, got, want, settled_below):
+    """Focused plans (tasi_set_focus): values below settled_below are final, the others upper bounds."""
+    m = want < settled_below
+    assert np.array_equal(np.isfinite(got[m]), np.isfinite(want[m]))
+    if kind == 1:
+        assert (np.abs(got[m] - want[m]) / np.maximum(want[m], 1e-30)).max(initial=0.0) <= REL_TOL
+    else:
+        assert np.array_equal(got[m], want[m])
+    fin = np.isfinite(want)
+    assert np.all(got[fin] >= want[fin] * (1 - 1e-5 if kind == 1 else 1.0)) and np.all(np.isinf(got[~fin]))
+
+
+@pytest.mark.parametrize("focus", [False, True])
+@pytest.mark.parametrize("kind", KINDS)
+@pytest.mark.parametrize("seed", [0, 1, 2])
+def test_random_patch_sequences(oracle, kind, seed, focus):
+    """A drive of random events — patches anywhere (borders, overlapping, two before one step, the whole map, walls
+    that cut the goal off and patches that reopen it), moved starts, a changed goal — after every step the field is
+    the from-scratch field of the map as it then is."""
+    import random
+    rng = random.Random(1000 * kind + seed)
+    L, W = rng.choice([(97, 130), (160, 75), (129, 129)])
+    start, goal = (3.0, 4.0), (float(L - 5), float(W - 7))
+    cmap = synth.synth_map(50 + seed, L, W, rng.choice([0, 10, 20]), start, goal)
+    p = plan(kind, cmap, start, goal)
+    compare(kind, p.read_field(), oracle.solve(kind, cmap, goal))
+    p.set_focus(focus, 0.0)  # focused: every later step stops once its start is settled and parks the rest
+    for step in range(9):
+        for _ in range(rng.choice([1, 1, 2])):
+            what = rng.randrange(6)
+            if what == 0:  # the whole map re-drawn
+                x = y = 0
+                patch = synth.synth_rows(900 + step, 0, L, W, rng.choice([5, 15]))
+            elif what == 1:  # a wall across the map (may cut the goal off), with or without a door
+                x, y = rng.randrange(10, L - 10), 0
+                patch = np.full((2, W), 255, np.uint8)
+                if rng.random() < 0.5:
+                    patch[:, rng.randrange(W - 3):][:, :3] = 7
+            elif what == 2:  # everything cheap again in a big block (reopens, lowers)
+                h, w = rng.randrange(20, L), rng.randrange(20, W)
+                x, y = rng.randrange(L - h + 1), rng.randrange(W - w + 1)
+                patch = np.full((h, w), rng.randrange(1, 9), np.uint8)
+            else:  # a random block, often touching a border
+                h, w = rng.randrange(1, 50), rng.randrange(1, 50)
+                x = rng.choice([0, L - h, rng.randrange(L - h + 1)])
+                y = rng.choice([0, W - w, rng.randrange(W - w + 1)])
+                patch = synth.synth_rows(7000 + 31 * step + what, 0, h, w, rng.choice([0, 20, 60]))
+            p.patch_map(patch, x, y)
+            oracle.patch(cmap, patch, x, y)
+        if step == 5:
+            goal = (float(rng.randrange(5, L - 5)), float(rng.randrange(5, W - 5)))
+            p.set_goal(*goal)
+        p.set_start(float(rng.randrange(1, L - 1)), float(rng.randrange(1, W - 1)))
+        assert p.step() == 0
+        assert np.array_equal(p.read_map(), cmap)
+        if focus:
+            compare_settled(kind, p.read_field(), oracle.solve(kind, cmap, goal), p.stats()["settled_below"])
+        else:
+            compare(kind, p.read_field(), oracle.solve(kind, cmap, goal))
+    p.set_focus(False)
+    p.set_start(1.0, 1.0)
+    assert p.step() == 0  # whatever was parked is finished now
+    compare(kind, p.read_field(), oracle.solve(kind, cmap, goal))
+    p.close()

@@ -11,6 +11,8 @@ import random
 import numpy as np
 import pytest
 
+import hostops
+
 from unige_tasi_path_planners_b200 import _lib, synth
 
 GOLDEN = os.path.join(os.path.dirname(__file__), "golden", "paths.npz")
@@ -44,7 +46,7 @@ def test_golden_file_covers_all_planners_and_options():
 
 def test_host_walk_equals_golden():
     for c in golden_cases():
-        xy, sc, cost, dist, rc = _lib.host_extract(c["kind"] == 1, c["field"], c["cmap"], c["start"], c["goal"], 255,
+        xy, sc, cost, dist, rc = hostops.host_extract(c["kind"] == 1, c["field"], c["cmap"], c["start"], c["goal"], 255,
                                                    c["max_steps"], c["lookahead"], c["indirect"])
         same_walk(c, xy, sc, cost, dist, "golden case %d" % c["i"])
         reached = tuple(xy[-1]) == c["goal"]
@@ -82,7 +84,7 @@ def test_host_walk_equals_reference_extractor(oracle):
                 ms = 20 if (seed + la + ind) % 2 else 500
                 xy, cost, dist, _ = r.extract(field=field, max_steps=ms, lookahead=la, allow_indirect=ind)
                 c = dict(path=xy, costs=r.step_costs(), totals=np.array([cost, dist], np.float32))
-                got = _lib.host_extract(kind == 1, field, cmap, start, goal, 255, ms, la, ind)
+                got = hostops.host_extract(kind == 1, field, cmap, start, goal, 255, ms, la, ind)
                 same_walk(c, *got[:4], "kind %d seed %d lookahead %d indirect %d" % (kind, seed, la, ind))
                 n += 1
         r.close()
@@ -94,12 +96,12 @@ def test_walk_respects_the_occupancy_threshold_and_capacity(oracle):
     cmap[:, 8] = 200  # a wall once the threshold drops below 200
     field = np.full((17, 17), np.inf, np.float32)
     field[:, 9:] = 10.0 * np.abs(np.arange(9, 17) - 12)[None, :] + 10.0 * np.abs(np.arange(17) - 8)[:, None]
-    xy, _, _, _, rc = _lib.host_extract(False, field, cmap, (8.0, 4.0), (8.0, 12.0), thr=128)
+    xy, _, _, _, rc = hostops.host_extract(False, field, cmap, (8.0, 4.0), (8.0, 12.0), thr=128)
     assert rc == 2 and len(xy) == 1  # every node around the start is unreached: stuck
     field = oracle.solve(0, cmap, (8.0, 12.0))
-    xy, _, _, _, rc = _lib.host_extract(False, field, cmap, (8.0, 2.0), (8.0, 12.0), thr=255, cap=4)
+    xy, _, _, _, rc = hostops.host_extract(False, field, cmap, (8.0, 2.0), (8.0, 12.0), thr=255, cap=4)
     assert rc == 3 and len(xy) <= 4
-    xy, _, _, _, rc = _lib.host_extract(False, field, cmap, (8.0, 2.0), (8.0, 12.0), thr=255)
+    xy, _, _, _, rc = hostops.host_extract(False, field, cmap, (8.0, 2.0), (8.0, 12.0), thr=255)
     assert rc == 0 and tuple(xy[-1]) == (8.0, 12.0)
 
 
@@ -134,7 +136,7 @@ def test_gpu_walk_equals_host_walk_and_reference(oracle):
                 res, _ = p.extract_paths(None, None, ms, la, ind)
                 g = res[0]
                 what = "kind %d seed %d lookahead %d indirect %d" % (kind, seed, la, ind)
-                h = _lib.host_extract(kind == 1, field, cmap, start, goal, 255, ms, la, ind)
+                h = hostops.host_extract(kind == 1, field, cmap, start, goal, 255, ms, la, ind)
                 c = dict(path=h[0], costs=h[1], totals=np.array(h[2:4], np.float32))
                 same_walk(c, g["path"], g["costs"], g["total_cost"], g["total_dist"], what + " (host walk)")
                 assert g["status"] == h[4]
@@ -177,7 +179,7 @@ def test_gpu_batch_of_walks_equals_single_walks():
     many, _ = p.extract_paths(starts, goals, 4000)
     field = p.read_field()
     for s, m in zip(starts, many):
-        one = _lib.host_extract(False, field, cmap, s, goal, 255, 4000)
+        one = hostops.host_extract(False, field, cmap, s, goal, 255, 4000)
         assert np.array_equal(m["path"], one[0]) and np.array_equal(m["costs"], one[1])
         assert m["status"] == one[4] and np.float32(m["total_cost"]) == np.float32(one[2])
     assert sum(m["status"] == 0 for m in many) >= 30

@@ -11,6 +11,8 @@ import threading
 import numpy as np
 import pytest
 
+import hostops
+
 from unige_tasi_path_planners_b200 import _lib, build, synth
 
 KINDS = {"fd": 0, "dfm": 1, "mfd": 2}
@@ -142,7 +144,7 @@ def test_fifo_drive_to_the_goal(exe, oracle, kind, focus, tmp_path):
         assert np.allclose(path[0], p0, atol=1e-5, rtol=0)  # (the float32 "+ 0.5" of the DFM report is not exactly undone)
         p0 = (float(path[0][0]), float(path[0][1]))
         want = oracle.solve(k, kmap, goal)
-        hw = _lib.host_extract(k == 1, want, kmap, p0, goal, 255, 20, True, indirect)
+        hw = hostops.host_extract(k == 1, want, kmap, p0, goal, 255, 20, True, indirect)
         if k != 1:
             assert np.array_equal(path, hw[0]), "step %d" % i
             assert np.array_equal(costs[:len(hw[1])], hw[1]) and not costs[len(hw[1]):].any()

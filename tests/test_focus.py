@@ -10,6 +10,8 @@ the field exactly.
 import numpy as np
 import pytest
 
+import hostops
+
 from unige_tasi_path_planners_b200 import _lib, synth
 
 pytestmark = pytest.mark.gpu
@@ -67,7 +69,7 @@ def test_focused_plan_settles_up_to_the_start_and_resumes(oracle, kind):
     assert 0 < n < want.size / 2
     # the walk from the start reads settled values only where it matters: same walk as over the converged field
     res, _ = p.extract_paths(None, None, 20)
-    hw = _lib.host_extract(kind == 1, want, cmap, start, goal, 255, 20)
+    hw = hostops.host_extract(kind == 1, want, cmap, start, goal, 255, 20)
     if kind != 1:
         assert np.array_equal(res[0]["path"], hw[0])
     assert res[0]["total_cost"] == pytest.approx(hw[2], rel=1e-3)
@@ -127,7 +129,7 @@ def test_focused_demo_loop_with_patches(oracle, kind):
             break
         check_settled(kind, p.read_field(), want, st["settled_below"], pos)
         res, _ = p.extract_paths(None, None, 20)
-        hw = _lib.host_extract(kind == 1, want, known, pos, goal, 255, 20)
+        hw = hostops.host_extract(kind == 1, want, known, pos, goal, 255, 20)
         if kind != 1:
             assert np.array_equal(res[0]["path"], hw[0]), "iteration %d" % it
             assert res[0]["total_cost"] == pytest.approx(hw[2], rel=1e-3)

@@ -6,6 +6,8 @@ Bars (BASELINE.json north_star): reachability masks identical; FD*/MFD* fields b
 import numpy as np
 import pytest
 
+import hostops
+
 from unige_tasi_path_planners_b200 import synth
 
 pytestmark = pytest.mark.gpu
@@ -228,7 +230,7 @@ def test_stacked_batch_equals_single_plans(oracle, kind):
     sb.plan(maps, goals)
     walks, _ = sb.paths(starts, 2000, with_costs=True)
     for i, (m, s, g) in enumerate(zip(maps, starts, goals)):
-        hw = _lib.host_extract(kind == 1, sb.field(i), m, s, g, 255, 2000)
+        hw = hostops.host_extract(kind == 1, sb.field(i), m, s, g, 255, 2000)
         assert np.array_equal(walks[i]["path"], hw[0]) and np.array_equal(walks[i]["costs"], hw[1]), i
         assert walks[i]["status"] == hw[4] and (kind == 1 or hw[4] == 0)
     # a replan on the stack: patch map 1's block, every block still equals its own from-scratch plan

@@ -13,6 +13,8 @@ import subprocess
 import numpy as np
 import pytest
 
+import hostops
+
 from unige_tasi_path_planners_b200 import build, synth
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -90,7 +92,7 @@ def test_plan_demo_matches_oracle(demo, oracle, kind, tmp_path):
         # GpuPathExtractor (device walk, reference defaults) == the same walk on the host over the dumped field
         from unige_tasi_path_planners_b200 import _lib
         path = np.fromfile(dump + "." + what + ".path", np.float32).reshape(-1, 2)
-        hw = _lib.host_extract(k == 1, got, cm, start if what == "plan" else (8.0, 8.0), goal, 255, 20)
+        hw = hostops.host_extract(k == 1, got, cm, start if what == "plan" else (8.0, 8.0), goal, 255, 20)
         assert np.array_equal(path, hw[0])
         line = lines[0 if what == "plan" else 1]
         assert line["path_points"] == len(path) and line["path_cost"] == pytest.approx(hw[2], rel=1e-6)

@@ -10,6 +10,8 @@ the minimum is unique; where they differ the reference's triangle must tie.
 import numpy as np
 import pytest
 
+import hostops
+
 from unige_tasi_path_planners_b200 import _lib, synth
 
 NBR8 = [(-1, 0), (-1, -1), (0, -1), (1, -1), (1, 0), (1, 1), (0, 1), (-1, 1)]  # Graph::neighbors_8 order
@@ -28,13 +30,13 @@ def test_node_parents_attain_the_value_and_match_the_reference(oracle, kind):
     checked = same = ties = 0
     for seed, cmap, start, goal in cases():
         F = oracle.solve(kind, cmap, goal)
-        par = _lib.host_parents(kind, F, cmap)
+        par = hostops.host_parents(kind, F, cmap)
         fin = np.isfinite(F) & (F > 0)
         assert not par[~fin].any()                      # goals and unreached nodes have no parents
         assert np.all(par[fin][:, :2].any(axis=1)) and np.all(par[fin][:, 2:].any(axis=1))
         xs, ys = np.nonzero(fin)
         for x, y in list(zip(xs, ys))[::7]:
-            tri = _lib.host_node_triangles(kind, F, cmap, x, y)
+            tri = hostops.host_node_triangles(kind, F, cmap, x, y)
             k = NBR8.index((int(par[x, y, 0]), int(par[x, y, 1])))
             assert NBR8[(k + 7) & 7] == (int(par[x, y, 2]), int(par[x, y, 3]))  # second parent = ccw(b)
             assert tri[k] == F[x, y] == tri.min()
@@ -52,7 +54,7 @@ def test_node_parents_attain_the_value_and_match_the_reference(oracle, kind):
             if b == (int(par[x, y, 0]), int(par[x, y, 1])):
                 same += 1
             else:
-                tri = _lib.host_node_triangles(kind, F, cmap, x, y)
+                tri = hostops.host_node_triangles(kind, F, cmap, x, y)
                 assert tri[NBR8.index(b)] == F[x, y], "reference parent of (%d,%d) is not a minimum" % (x, y)
                 ties += 1
         r.close()
@@ -70,7 +72,7 @@ def test_cell_parents_match_the_reference(oracle):
         r.step()
         info = r.dump_info()
         closed, g = r.closed_mask()
-        par = _lib.host_parents(1, np.where(closed, g, np.inf).astype(np.float32), cmap)
+        par = hostops.host_parents(1, np.where(closed, g, np.inf).astype(np.float32), cmap)
         # parents read settled neighbours only: compare where the whole neighbourhood is closed
         inner = closed.copy()
         for dx, dy in NBR8:
@@ -101,7 +103,7 @@ def test_gpu_parents_equal_host_parents(kind):
         assert p.step() == 0
         F = p.read_field()
         got = p.read_parents()
-        assert np.array_equal(got, _lib.host_parents(kind, F, cmap))
+        assert np.array_equal(got, hostops.host_parents(kind, F, cmap))
         w = p.read_parents(5, 7, 11, 13)
         assert np.array_equal(w, got[5:16, 7:20])
         with pytest.raises(Exception):

@@ -297,6 +297,7 @@ __device__ inline void drain_and_advance(const GridDesc &d, int *s_red, int *s_a
 constexpr int IN_N = 1, IN_S = 2, IN_W = 4, IN_E = 8, IN_NW = 16, IN_NE = 32, IN_SW = 64, IN_SE = 128, IN_ALL = 256;
 constexpr int WIN_R = 3;          // a strip of SW elements reads a 3 x (SW + 2) window
 constexpr int MAX_WARPS = 16;     // per CTA, over the kernel instances (SW = 2: 512 threads)
+constexpr int LEAVE_TID = 32;     // the thread that releases the tile after a visit (first lane of warp 1)
 
 template <int KIND, int SW>
 __device__ __forceinline__ float eval_strip_elem(const float (&w)[WIN_R][SW + 2], const float (&cw)[2][SW + 1], int j) {
@@ -584,7 +585,9 @@ __global__ void __launch_bounds__(1024 / SW, SW == 4 ? 2 : 1) solver_kernel(Grid
                 if (ecol) atomicMin(&s_kmin[3], klast);
             }
             __syncthreads();
-            if (tid < 9) fence_gpu();  // the CTA's write-back (ordered by the barrier) before the flags below
+            // the CTA's write-back (ordered by the barrier) before the flags below; the leaving thread sits in another
+            // warp than the activating ones, so its atomics overlap theirs instead of following them
+            if (tid < 8 || tid == LEAVE_TID) fence_gpu();
 
             // activate the neighbours that read a changed border, one thread per direction
             // (0 N, 1 S, 2 W, 3 E, 4 NW, 5 NE, 6 SW, 7 SE); our north border is the south halo of the tile above
@@ -598,8 +601,8 @@ __global__ void __launch_bounds__(1024 / SW, SW == 4 ? 2 : 1) solver_kernel(Grid
                 const int nx = tx + dx, ny = ty + dy;
                 if (k != INF_BITS && nx >= 0 && nx < d.TX && ny >= 0 && ny < d.TY) activate(d, nx * d.TY + ny, k, seen_as);
             }
-            // ... while thread 8 leaves the tile (a neighbour may re-queue it at once: we no longer touch its values)
-            if (tid == 8) {
+            // ... while thread 32 leaves the tile (a neighbour may re-queue it at once: we no longer touch its values)
+            if (tid == LEAVE_TID) {
                 if (MODE == 1) d.seed[tile] = 1;  // phase 2 revisits every tile phase 1 looked at
                 // leave the tile, unless a neighbour changed our halo meanwhile
                 int again_f = 0;

@@ -117,23 +117,28 @@ __device__ inline void q_push(const GridDesc &d, int tile) {
     atomicExch(&d.queue[(unsigned) t & d.qmask], tile + 1);
 }
 
+#ifndef Q_SLEEP_MAX_NS
+#define Q_SLEEP_MAX_NS 256
+#endif
 __device__ inline int q_pop(const GridDesc &d) {
     unsigned long long t = atomicAdd(&d.ctl->head, 1ULL);
     volatile int *slot = &d.queue[(unsigned) t & d.qmask];
     volatile int *done = &d.ctl->done;
     unsigned long long t0 = 0;
-    unsigned ns = 32;
+    unsigned ns = 32, polls = 0;
     for (;;) {
         int v = *slot;
         if (v != 0) {
             *slot = 0;
             return v - 1;
         }
-        if (*done) return -1;
+        // the slot is this ticket's own word; `done` shares its line with the queue counters, so it is looked at
+        // on every fourth poll only and the back-off can stay short (a waiting CTA sits on the critical path)
+        if ((++polls & 3u) == 0 && *done) return -1;
         if (t0 == 0) t0 = globaltimer_ns();
         else if (globaltimer_ns() - t0 > d.ctl->timeout_ns) { q_fail(d); return -1; }
         __nanosleep(ns);
-        if (ns < 1024) ns <<= 1;
+        if (ns < Q_SLEEP_MAX_NS) ns <<= 1;
     }
 }
 

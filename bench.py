@@ -26,9 +26,19 @@ import sys
 import threading
 import time
 
-# rank 0 prints ONE JSON line on stdout: NCCL's version banner (NCCL_DEBUG=VERSION, set on some boxes) goes there too
-if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+# rank 0 prints ONE JSON line on stdout. NCCL writes its version banner to file descriptor 1 as well (NCCL_DEBUG=VERSION
+# from the environment or from /etc/nccl.conf), so descriptor 1 is pointed at stderr for the whole run and the JSON
+# line goes to a copy of the original stdout.
+if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
     os.environ["NCCL_DEBUG"] = "WARN"
+sys.stdout.flush()
+_JSON_FD = os.dup(1)
+os.dup2(2, 1)
+
+
+def emit(line):
+    sys.stdout.flush()
+    os.write(_JSON_FD, (json.dumps(line) + "\n").encode())
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
@@ -180,7 +190,7 @@ def run_reference(args, rank):
                              "sample": cpu_sample_desc(side, kind), "host_cpus": os.cpu_count()},
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def cpu_baseline():
@@ -318,7 +328,7 @@ def run_b200(args, rank, world):
                 "clocks": clocks}
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline()
-        print(json.dumps(line), flush=True)
+        emit(line)
     p.close()
     if world > 1:
         dist.destroy_process_group()

@@ -27,18 +27,18 @@ import threading
 import time
 
 # rank 0 prints ONE JSON line on stdout. NCCL writes its version banner to file descriptor 1 as well (NCCL_DEBUG=VERSION
-# from the environment or from /etc/nccl.conf), so descriptor 1 is pointed at stderr for the whole run and the JSON
-# line goes to a copy of the original stdout.
+# from the environment or from /etc/nccl.conf), so descriptor 1 is pointed at stderr for the whole run and Python's
+# sys.stdout (the JSON line) writes to a copy of the original stdout.
 if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
     os.environ["NCCL_DEBUG"] = "WARN"
 sys.stdout.flush()
 _JSON_FD = os.dup(1)
 os.dup2(2, 1)
+sys.stdout = os.fdopen(_JSON_FD, "w")  # Python-level prints (the JSON line of every workload) keep the real stdout
 
 
 def emit(line):
-    sys.stdout.flush()
-    os.write(_JSON_FD, (json.dumps(line) + "\n").encode())
+    print(json.dumps(line), flush=True)
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:

@@ -197,8 +197,9 @@ int alloc_grid(tasi_planner *p, int W, int rows) {
     // active tiles than SMs x a few. There ONE CTA per SM with 512 threads and 2-element strips halves the serial
     // work of a thread per round and beats two 256-thread CTAs per SM; from some grid size on the second CTA's
     // extra tile in flight wins. Measured cross-over (tiles), per operator weight (scripts/quick_bench.py with
-    // TASI_STRIP=2|4; FD* 4096^2 34.1 -> 30.0 ms, 8192^2 97 -> 86 ms; MFD* 4096^2 21.5 -> 18.0 ms; MS-DFM 2048^2 8.4 -> 8.1):
-    const int strip2_upto = p->kind == TASI_FD ? 100000 : (p->kind == TASI_MFD ? 70000 : 4200);
+    // TASI_STRIP=2|4; FD* 4096^2 34.1 -> 30.0 ms, 8192^2 97 -> 86 ms; MFD* 4096^2 21.5 -> 18.0 ms; MS-DFM 2048^2 8.4 -> 8.1;
+    // re-measured after the in-strip Gauss-Seidel order: MFD* 8192^2 is 52.9 ms with 2-element strips, 46.4 ms with 4):
+    const int strip2_upto = p->kind == TASI_FD ? 100000 : (p->kind == TASI_MFD ? 33000 : 4200);
     p->strip = nt <= strip2_upto ? 2 : 4;
     if (const char *e = getenv("TASI_STRIP")) {
         const int v = atoi(e);

@@ -26,10 +26,11 @@ import sys
 import threading
 import time
 
-# rank 0 prints ONE JSON line on stdout. NCCL writes its version banner to file descriptor 1 as well (NCCL_DEBUG=VERSION
-# from the environment or from /etc/nccl.conf), so descriptor 1 is pointed at stderr for the whole run and Python's
-# sys.stdout (the JSON line) writes to a copy of the original stdout.
-if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+# rank 0 prints ONE JSON line on stdout. NCCL writes its version banner and its INFO lines to file descriptor 1 as well
+# (NCCL_DEBUG from the environment or from /etc/nccl.conf), so descriptor 1 is pointed at stderr for the whole run and
+# Python's sys.stdout (the JSON line) writes to a copy of the original stdout. An NCCL_DEBUG the caller has set is
+# left as it is (the driver's INFO setting is its evidence of the ranks); only an unset one becomes WARN.
+if "NCCL_DEBUG" not in os.environ:
     os.environ["NCCL_DEBUG"] = "WARN"
 sys.stdout.flush()
 _JSON_FD = os.dup(1)
@@ -62,6 +63,8 @@ def parse():
     ap.add_argument("--workload", default="cfg2", choices=["cfg2", "cfg3", "cfg5", "bands"])
     ap.add_argument("--side", type=int, default=N_SIDE, help="grid side (development only; the contract is 4096)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true",
+                    help="cfg2 only: skip the replan (cfg3), batch (cfg5) and bands (cfg4) records of the line")
     ap.add_argument("--full", action="store_true", help="cfg5: the full 64 maps x 64 queries instead of a sample")
     return ap.parse_args()
 
@@ -132,16 +135,19 @@ class ClockSampler:
 
 
 # ---- the CPU side: the unmodified reference (oracle/_ref) or, without it, the oracle port ------------------
-def cpu_plan_once(side, seed):
+def cpu_plan_once(side, seed, fast=True):
     """One MS-DFM initial plan on the CPU on a side x side grid of the bench's generator.
-    Returns (seconds, kind): kind "reference" = oracle/_ref (the reference's own DFMPlanner<1>, its p_time),
-    "port" = oracle/tasi_oracle.c heap solver (wall clock)."""
+    Returns (seconds, kind, build): kind "reference" = oracle/_ref (the reference's own DFMPlanner<1>, its p_time),
+    "port" = oracle/tasi_oracle.c heap solver (wall clock). build = which of the two reference builds ran: the timing
+    build (the reference's Release flags, oracle/Makefile REF_FAST_FLAGS) when this CPU can run it, else the parity
+    build (-ffp-contract=off)."""
     from oracle import oracle_py as O  # CPU baseline leg: the one place bench.py executes oracle/
     from unige_tasi_path_planners_b200 import synth
     start, goal = synth.default_endpoints(side, side)
     cmap = synth.synth_map(seed, side, side, P_OBS, start, goal)
     if O.ref_available():
-        r = O.RefPlanner(KIND_DFM, 1)
+        use_fast = bool(fast and O.ref_fast_available(KIND_DFM))
+        r = O.RefPlanner(KIND_DFM, 1, fast=use_fast)
         r.set_map(cmap, 1.0)
         r.set_start(*start)
         r.set_goal(*goal)
@@ -149,45 +155,53 @@ def cpu_plan_once(side, seed):
         u_ms, p_ms = r.times()
         r.close()
         assert rc == 0
-        return (u_ms + p_ms) / 1e3, "reference"
+        return (u_ms + p_ms) / 1e3, "reference", ("-O2 -march=x86-64-v3 -DNDEBUG" if use_fast else
+                                                  "-O2 -ffp-contract=off -DNDEBUG")
     t0 = time.perf_counter()
     O.solve(KIND_DFM, cmap, goal, method="heap")
-    return time.perf_counter() - t0, "port"
+    return time.perf_counter() - t0, "port", "gcc -O2 -ffp-contract=off"
 
 
-def cpu_sample_desc(side, kind):
-    what = ("the reference's DFMPlanner<1> (oracle/_ref, built from the unmodified sources, -O2 -ffp-contract=off, "
-            "NO_HEURISTIC), its own u_time+p_time") if kind == "reference" else \
-           "oracle/tasi_oracle.c heap solver (CPU restatement), wall clock"
+def cpu_sample_desc(side, kind, build):
+    what = ("the reference's DFMPlanner<1> (oracle/_ref, built from the unmodified sources with %s, NO_HEURISTIC), "
+            "its own u_time+p_time" % build) if kind == "reference" else \
+           "oracle/tasi_oracle.c heap solver (CPU restatement, %s), wall clock" % build
     return "MS-DFM initial plan on a %dx%d grid of the same generator (seed 1, 10%% obstacles), 1 thread: %s" % (
         side, side, what)
 
 
 def run_reference(args, rank):
-    """--impl reference: the reference's CPU planner on the host cores, bounded sample per step. The reference is
-    single-threaded, so `cores` is 1; rank 0 alone runs."""
+    """--impl reference: the reference's CPU planner on the host cores on the SAME workload as the B200 arm: the full
+    4096 x 4096 grid of cfg2. The reference is single-threaded, so `cores` is 1; rank 0 alone runs.
+    A plan takes 45-75 s on one core, so min(steps, 3) full-size plans are timed (fewer if 150 s have passed) and the
+    line says how many; the rate of a bounded 1536^2 sample is reported beside it."""
     if rank != 0:
         return
-    # keep the whole run within a few minutes whatever K is: ~0.36 Mcells/s on one core
-    side = REF_SAMPLE_SIDE
-    while side > 256 and args.steps * side * side / 0.24e6 > 200.0:
-        side -= 128
-    kind = "reference"
+    side = args.side
+    kind, build = "reference", ""
     for _ in range(max(args.warmup, 0) and 1):  # one warm-up plan is enough to page the libraries in
-        _, kind = cpu_plan_once(256, 1)
-    tot = 0.0
-    for _ in range(args.steps):
-        dt, kind = cpu_plan_once(side, 1)
+        _, kind, build = cpu_plan_once(256, 1)
+    dt_s, _, _ = cpu_plan_once(REF_SAMPLE_SIDE, 1)
+    tot, n = 0.0, 0
+    t_begin = time.perf_counter()
+    for _ in range(max(1, min(args.steps, 3))):
+        dt, kind, build = cpu_plan_once(side, 1)
         tot += dt
-    ms = tot / args.steps * 1e3
+        n += 1
+        if time.perf_counter() - t_begin > 150.0:
+            break
+    ms = tot / n * 1e3
     val = side * side / (ms / 1e3) / 1e6
     line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "cfg2", "planner": "MS-DFM level 1", "grid": "%dx%d sample of the 4096x4096 "
-                       "workload" % (side, side), "p_obs": P_OBS},
+            "config": {"workload": "cfg2", "planner": "MS-DFM (DFMPlanner level 1)", "grid": "%dx%d" % (side, side),
+                       "p_obs": P_OBS, "seed": 1, "plans_timed": n,
+                       "note": "the full cfg2 grid, %d plan(s) timed out of the %d steps asked for (a plan takes about a "
+                               "minute on one core)" % (n, args.steps),
+                       "sample_1536": {"mcells_per_s": REF_SAMPLE_SIDE ** 2 / dt_s / 1e6, "seconds": dt_s}},
             "cpu_baseline": {"value": val, "unit": UNIT, "cores": 1, "kind": kind,
-                             "sample": cpu_sample_desc(side, kind), "host_cpus": os.cpu_count()},
+                             "sample": cpu_sample_desc(side, kind, build), "host_cpus": os.cpu_count()},
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     emit(line)
@@ -196,9 +210,9 @@ def run_reference(args, rank):
 def cpu_baseline():
     """Bounded CPU sample timed beside the GPU number (rank 0, N = 1)."""
     cpu_plan_once(128, 1)
-    dt, kind = cpu_plan_once(REF_SAMPLE_SIDE, 1)
+    dt, kind, build = cpu_plan_once(REF_SAMPLE_SIDE, 1)
     return {"value": REF_SAMPLE_SIDE * REF_SAMPLE_SIDE / dt / 1e6, "unit": UNIT, "cores": 1, "kind": kind,
-            "sample": cpu_sample_desc(REF_SAMPLE_SIDE, kind), "seconds": dt, "host_cpus": os.cpu_count()}
+            "sample": cpu_sample_desc(REF_SAMPLE_SIDE, kind, build), "seconds": dt, "host_cpus": os.cpu_count()}
 
 
 # ---- the B200 arm --------------------------------------------------------------------------------------------
@@ -298,6 +312,29 @@ def run_b200(args, rank, world):
     if world > 1:
         dist.all_reduce(tm, op=dist.ReduceOp.MAX)
     dev_ms_max, e2e_ms_max, wall_ms_max = [float(v) for v in tm.tolist()]
+    p.close()
+    del flush, host_map, out
+    torch.cuda.empty_cache()
+
+    # ---- the rest of BASELINE.json's metric in the same line: replan latency (cfg3, N = 1), the query batch (cfg5)
+    # and the row-band sharded grid (cfg4 shape, strong scaling) — each measured by its own module, outside cfg2's
+    # timed region
+    extras = {}
+    if not args.no_extras and side == N_SIDE:
+        peak_gbs, _ = measured_peak_gbs()
+        if world == 1:
+            from unige_tasi_path_planners_b200 import replan_bench
+            extras["replan"] = replan_bench.measure(16384, max(1, min(args.steps, 5)), 1, local, peak_gbs,
+                                                    variants=("mixed", "raise", "lower"))
+            torch.cuda.empty_cache()
+        from unige_tasi_path_planners_b200 import batch
+        res, cfg = batch.measure(rank, world, local, 1024, False)
+        extras["batch"] = {"config": cfg, "queries_per_s": {k: v["queries_per_s"] for k, v in res.items()},
+                           "mcells_per_s": {k: v["mcells_per_s"] for k, v in res.items()},
+                           "verified": all(v["reached"] == v["queries"] for v in res.values()),
+                           "verified_how": "every query's start has a finite value (endpoints are free cells)",
+                           "per_planner": res}
+        torch.cuda.empty_cache()
     if rank == 0:
         ms_per_step = dev_ms_max / args.steps
         value = world * cells / (ms_per_step / 1e3) / 1e6
@@ -316,7 +353,10 @@ def run_b200(args, rank, world):
                            "stream inside tasi_step; wall %.2f ms/step" % (wall_ms_max / args.steps)},
                 "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": cells,
                         "d2h_bytes_per_step": win * win * 4, "ms_per_step": e2e_ms_max / args.steps,
-                        "what": "set_map(host) + set_start + set_goal + step + read_window(64x64 at start)",
+                        "what": "set_map(host) + set_start + set_goal + step + read_window(64x64 at start): the hand-off "
+                                "the path extractor consumes; GpuPathExtractor (the default hand-off of the C++ classes) "
+                                "walks on the device and only the path crosses the bus. Reading the WHOLE field back "
+                                "costs full_field_d2h_ms on top",
                         "full_field_d2h_ms": full_read_ms},
                 "gpu_launches": launches,
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
@@ -326,10 +366,10 @@ def run_b200(args, rank, world):
                 "work": {"tiles": tiles, "tile_visits_per_tile": visits / args.steps / tiles,
                          "elem_evals_per_cell": evals / args.steps / cells},
                 "clocks": clocks}
+        line.update(extras)
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline()
         emit(line)
-    p.close()
     if world > 1:
         dist.destroy_process_group()
 

@@ -49,7 +49,10 @@ typedef struct tasi_stats {
     uint64_t queue_pushes;     /* tile activations that entered the work queue */
     uint64_t inval_visits;     /* tile visits of the invalidate phase of a replan */
     uint64_t elem_invalidated; /* elements reset to INF by the invalidate phase */
-    uint64_t seed_elems;       /* elements seeded by the last patch (== num_nodes_updated) */
+    uint64_t seed_elems;       /* elements seeded by the patches pending at this step (== num_nodes_updated). Deviation
+                                * from Graph::update (Graph.cpp:36-51), which clears updated_cells_ on every patch and so
+                                * seeds the LAST patch only: every patch since the last consumed replan is seeded, and
+                                * the counter is the sum over them (an element touched by two patches counts twice) */
     uint64_t phases;           /* advances of the near/far threshold (tile-level Delta-stepping) */
     uint64_t far_parked;       /* activations parked in the far pile */
     float kernel_ms_solve;     /* CUDA-event time of the solver kernel(s), re-propagation phase */

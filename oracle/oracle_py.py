@@ -113,48 +113,65 @@ def ref_available():
     return all(os.path.exists(os.path.join(HERE, "_ref", n)) for n in _REF_LIB.values())
 
 
-def _ref_lib(kind):
-    if kind not in _ref_libs:
-        R = C.CDLL(os.path.join(HERE, "_ref", _REF_LIB[kind]))
-        R.ref_create.restype = C.c_void_p
-        R.ref_create.argtypes = [C.c_int]
-        R.ref_destroy.argtypes = [C.c_void_p]
-        R.ref_set_map.argtypes = [C.c_void_p, _u8p, C.c_int, C.c_int, C.c_float]
-        R.ref_patch_map.argtypes = [C.c_void_p, _u8p, C.c_int, C.c_int, C.c_int, C.c_int]
-        R.ref_set_start.argtypes = [C.c_void_p, C.c_float, C.c_float]
-        R.ref_set_goal.argtypes = [C.c_void_p, C.c_float, C.c_float]
-        R.ref_reset.argtypes = [C.c_void_p]
-        R.ref_step.restype = C.c_int
-        R.ref_step.argtypes = [C.c_void_p]
-        R.ref_times.argtypes = [C.c_void_p, _f32p, _f32p]
-        R.ref_counters.argtypes = [C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
-        R.ref_map_size.restype = C.c_uint64
-        R.ref_map_size.argtypes = [C.c_void_p]
-        R.ref_top_key.restype = C.c_float
-        R.ref_top_key.argtypes = [C.c_void_p, C.POINTER(C.c_int)]
-        R.ref_dump.argtypes = [C.c_void_p, _f32p, _f32p]
-        R.ref_dump_info.restype = C.c_int
-        R.ref_dump_info.argtypes = [C.c_void_p, C.POINTER(C.c_int32)]
-        R.ref_step_costs.restype = C.c_int
-        R.ref_step_costs.argtypes = [C.c_void_p, _f32p, C.c_int]
-        R.ref_extract.restype = C.c_int
-        R.ref_extract.argtypes = [C.c_void_p, C.c_int, _f32p, C.c_int, C.c_int, C.c_int, _f32p, C.c_int, _f32p,
-                                  _f32p, _f32p]
-        R.ref_op_tri.restype = C.c_float
-        R.ref_op_tri.argtypes = [C.c_void_p] + [C.c_int] * 6 + [C.c_float] * 2
-        R.ref_op_stencil.restype = C.c_float
-        R.ref_op_stencil.argtypes = [C.c_void_p] + [C.c_float] * 4
-        _ref_libs[kind] = R
-    return _ref_libs[kind]
+def ref_fast_available(kind=DFM):
+    """The timing build (-O2 -march=x86-64-v3 -DNDEBUG, oracle/Makefile) exists and this CPU can run it."""
+    if not os.path.exists(os.path.join(HERE, "_ref", _REF_LIB[kind].replace(".so", "_fast.so"))):
+        return False
+    try:
+        with open("/proc/cpuinfo") as f:
+            flags = next((l for l in f if l.startswith("flags")), "")
+    except OSError:
+        return False
+    fl = set(flags.split())
+    return {"avx2", "fma", "bmi2", "movbe"} <= fl
+
+
+def _ref_lib(kind, fast=False):
+    key = (kind, bool(fast))
+    if key in _ref_libs:
+        return _ref_libs[key]
+    name = _REF_LIB[kind].replace(".so", "_fast.so") if fast else _REF_LIB[kind]
+    R = C.CDLL(os.path.join(HERE, "_ref", name))
+    R.ref_create.restype = C.c_void_p
+    R.ref_create.argtypes = [C.c_int]
+    R.ref_destroy.argtypes = [C.c_void_p]
+    R.ref_set_map.argtypes = [C.c_void_p, _u8p, C.c_int, C.c_int, C.c_float]
+    R.ref_patch_map.argtypes = [C.c_void_p, _u8p, C.c_int, C.c_int, C.c_int, C.c_int]
+    R.ref_set_start.argtypes = [C.c_void_p, C.c_float, C.c_float]
+    R.ref_set_goal.argtypes = [C.c_void_p, C.c_float, C.c_float]
+    R.ref_reset.argtypes = [C.c_void_p]
+    R.ref_step.restype = C.c_int
+    R.ref_step.argtypes = [C.c_void_p]
+    R.ref_times.argtypes = [C.c_void_p, _f32p, _f32p]
+    R.ref_counters.argtypes = [C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+    R.ref_map_size.restype = C.c_uint64
+    R.ref_map_size.argtypes = [C.c_void_p]
+    R.ref_top_key.restype = C.c_float
+    R.ref_top_key.argtypes = [C.c_void_p, C.POINTER(C.c_int)]
+    R.ref_dump.argtypes = [C.c_void_p, _f32p, _f32p]
+    R.ref_dump_info.restype = C.c_int
+    R.ref_dump_info.argtypes = [C.c_void_p, C.POINTER(C.c_int32)]
+    R.ref_step_costs.restype = C.c_int
+    R.ref_step_costs.argtypes = [C.c_void_p, _f32p, C.c_int]
+    R.ref_extract.restype = C.c_int
+    R.ref_extract.argtypes = [C.c_void_p, C.c_int, _f32p, C.c_int, C.c_int, C.c_int, _f32p, C.c_int, _f32p,
+                              _f32p, _f32p]
+    R.ref_op_tri.restype = C.c_float
+    R.ref_op_tri.argtypes = [C.c_void_p] + [C.c_int] * 6 + [C.c_float] * 2
+    R.ref_op_stencil.restype = C.c_float
+    R.ref_op_stencil.argtypes = [C.c_void_p] + [C.c_float] * 4
+    _ref_libs[key] = R
+    return _ref_libs[key]
 
 
 class RefPlanner:
     """The reference planner `kind` (FD/DFM/MFD) at optimisation `level`, driven through its own public
     API (ReplannerBase.h:39-123)."""
 
-    def __init__(self, kind, level=1):
+    def __init__(self, kind, level=1, fast=False):
+        """fast: the timing build (never for parity: its float contraction is the compiler's choice)."""
         self.kind, self.level = kind, level
-        self.R = _ref_lib(kind)
+        self.R = _ref_lib(kind, fast)
         self.h = C.c_void_p(self.R.ref_create(level))
         if not self.h:
             raise ValueError("bad level %d for kind %d" % (level, kind))

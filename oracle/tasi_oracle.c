@@ -16,6 +16,8 @@
  * MFD* values live on the (L+1)x(W+1) nodes, MS-DFM values on the LxW cells.
  */
 #include <math.h>
+#include <pthread.h>
+#include <unistd.h>
 #include <stdint.h>
 #include <stdlib.h>
 #include <string.h>
@@ -258,19 +260,49 @@ uint64_t tasi_oracle_solve_heap(int kind, const uint8_t *map, int W, int L, int 
  * update of their neighbours (bit compare). 0 for a converged FD* / MFD* field. For MS-DFM
  * `n_above` (value below what the neighbours now give: the ulp-scale non-monotonicity noted in SURVEY.md
  * App. C.3) is reported separately; n_below must be 0 for any converged min-accept field. */
-void tasi_oracle_residual(int kind, const uint8_t *map, int W, int L, int thr, int gx, int gy, const float *g,
-                          uint64_t *n_below, uint64_t *n_above, float *max_rel) {
-    ctx_t c = {map, L, W, thr, kind == TASI_DFM ? L : L + 1, kind == TASI_DFM ? W : W + 1, g};
+typedef struct { int kind; const ctx_t *c; int gx, gy, x0, x1; uint64_t lo, hi; float mr; } res_job_t;
+
+static void *residual_rows(void *arg) {
+    res_job_t *j = (res_job_t *) arg;
+    const ctx_t *c = j->c;
     uint64_t lo = 0, hi = 0; float mr = 0.0f;
-    for (int x = 0; x < c.ex; ++x)
-        for (int y = 0; y < c.ey; ++y) {
-            if (x == gx && y == gy) continue;
-            float v = elem_update(kind, &c, x, y), s = g[(size_t) x * c.ey + y];
+    for (int x = j->x0; x < j->x1; ++x)
+        for (int y = 0; y < c->ey; ++y) {
+            if (x == j->gx && y == j->gy) continue;
+            float v = elem_update(j->kind, c, x, y), s = c->g[(size_t) x * c->ey + y];
             if (v == s) continue;
             if (v < s) ++lo; else ++hi;
             if (isfinite(v) && isfinite(s)) { float r = fabsf(v - s) / fabsf(s); if (r > mr) mr = r; }
             else mr = INFINITY;
         }
+    j->lo = lo; j->hi = hi; j->mr = mr;
+    return NULL;
+}
+
+/* rows are independent: blocks of rows go to up to 32 threads (the 16384^2 check of the config-size tests then takes
+ * seconds); TASI_ORACLE_THREADS overrides, 1 = the plain loop */
+void tasi_oracle_residual(int kind, const uint8_t *map, int W, int L, int thr, int gx, int gy, const float *g,
+                          uint64_t *n_below, uint64_t *n_above, float *max_rel) {
+    ctx_t c = {map, L, W, thr, kind == TASI_DFM ? L : L + 1, kind == TASI_DFM ? W : W + 1, g};
+    long nt = sysconf(_SC_NPROCESSORS_ONLN);
+    const char *e = getenv("TASI_ORACLE_THREADS");
+    if (e) nt = atol(e);
+    if (nt > 32) nt = 32;
+    if (nt < 1 || (size_t) c.ex * c.ey < (1u << 20)) nt = 1;
+    if (nt > c.ex) nt = c.ex;
+    res_job_t jobs[32];
+    pthread_t th[32];
+    for (int t = 0; t < nt; ++t) {
+        jobs[t] = (res_job_t){kind, &c, gx, gy, (int) ((int64_t) c.ex * t / nt), (int) ((int64_t) c.ex * (t + 1) / nt), 0, 0, 0.0f};
+        if (nt == 1) residual_rows(&jobs[t]);
+        else if (pthread_create(&th[t], NULL, residual_rows, &jobs[t]) != 0) { residual_rows(&jobs[t]); th[t] = 0; }
+    }
+    uint64_t lo = 0, hi = 0; float mr = 0.0f;
+    for (int t = 0; t < nt; ++t) {
+        if (nt > 1 && th[t]) pthread_join(th[t], NULL);
+        lo += jobs[t].lo; hi += jobs[t].hi;
+        if (jobs[t].mr > mr) mr = jobs[t].mr;
+    }
     *n_below = lo; *n_above = hi; *max_rel = mr;
 }
 

@@ -157,3 +157,39 @@ def test_focused_demo_loop_with_patches(oracle, kind):
     else:
         assert np.array_equal(got[fin], want[fin])
     p.close()
+
+
+@pytest.mark.parametrize("kind", KINDS)
+@pytest.mark.parametrize("slack", [0.0, -1.0])
+def test_focus_after_an_obstacle_block_next_to_the_start_opens_up(oracle, kind, slack):
+    """a block of believed obstacles thicker than a tile, next to the start, turns out free. The tiles of
+    the block hold nothing but INF, so their seed keys must come from their halo ring (seed_keys_kernel); keyed by
+    the interior alone they would sit in the pile with key INF, the focus test would fire with the shortcut through
+    the block never propagated, and the start would keep the cost of the way round."""
+    L = W = 320
+    goal, start = (260.0, 260.0), (58.0, 58.0)
+    cmap = np.full((L, W), 20, np.uint8)
+    cmap[64:192, 64:192] = 255  # 4 x 4 tiles of obstacles between the start and the goal
+    p = make(kind)
+    p.set_focus(True, slack)
+    p.set_map(cmap); p.set_start(*start); p.set_goal(*goal)
+    assert p.step() == 0
+    before = oracle.solve(kind, cmap, goal)
+    check_settled(kind, p.read_field(), before, p.stats()["settled_below"], start)
+    opened = cmap.copy()
+    opened[64:192, 64:192] = 1
+    p.patch_map(opened[64:192, 64:192], 64, 64)
+    p.set_start(*start)
+    assert p.step() == 0
+    st = p.stats()
+    want = oracle.solve(kind, opened, goal)
+    e0 = start_elems(kind, start)[0]
+    assert want[e0] < 0.8 * before[e0]  # the block really is a shortcut
+    got = p.read_field()
+    for e in start_elems(kind, start):
+        if kind == 1:
+            assert abs(got[e] - want[e]) <= 1e-4 * want[e], (e, got[e], want[e])
+        else:
+            assert got[e] == want[e], (e, got[e], want[e])
+    check_settled(kind, got, want, st["settled_below"], start)
+    p.close()

@@ -19,14 +19,24 @@ from . import planner as _planner
 from . import synth
 
 
-def make_queries(n_maps, per_map, side, seed=42):
-    """(map index, start, goal) triples: endpoints drawn uniformly, 9x9 blocks around them are cleared per map."""
+def make_queries(n_maps, per_map, side, seed=42, maps=None):
+    """(map index, start, goal) triples, endpoints drawn uniformly from the FREE cells of their map (SURVEY.md 8d;
+    rejection sampling with a seeded generator, so the batch is reproducible). `maps`: {index: uint8 array} of the maps
+    the queries run on; by default the generator's maps 1000 + index are built here."""
     rng = random.Random(seed)
     out = []
     for m in range(n_maps):
+        cmap = maps[m] if maps is not None and m in maps else synth.synth_map(1000 + m, side, side, 10, None, None)
+
+        def free_cell():
+            while True:
+                x, y = rng.randrange(8, side - 8), rng.randrange(8, side - 8)
+                if cmap[x, y] != 255:
+                    return (float(x), float(y))
+
         for _ in range(per_map):
-            s = (float(rng.randrange(8, side - 8)), float(rng.randrange(8, side - 8)))
-            g = (float(rng.randrange(8, side - 8)), float(rng.randrange(8, side - 8)))
+            s = free_cell()
+            g = free_cell()
             out.append((m, s, g))
     return out
 
@@ -128,25 +138,23 @@ class StackedBatch:
         self.p.close()
 
 
-def bench_main(args, rank, world):
+def measure(rank, world, local, side=1024, full=False, n_maps=None, per_map=None):
+    """The cfg5 record: a batch of independent (map, start, goal) queries, whole maps per rank, planned as stacked
+    multi-goal plans; wall clock of the whole batch, max over ranks. Collective: every rank of an initialised
+    torch.distributed group must call it. Returns (per-planner results, config dict)."""
     import torch
     import torch.distributed as dist
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py: no CUDA device — the product path has no CPU fallback")
-    local = int(os.environ.get("LOCAL_RANK", rank))
-    torch.cuda.set_device(local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    side = 1024 if args.side == 4096 else args.side
     lanes = int(os.environ.get("TASI_BATCH_LANES", "4"))
-    n_maps, per_map = (64, 64) if args.full else (8 * world, 16)
-    queries = make_queries(n_maps, per_map, side)
+    if n_maps is None:
+        n_maps, per_map = (64, 64) if full else (8 * world, 16)
+    # every rank builds every map of the batch (the draw of the endpoints needs them and has to be the same everywhere)
+    all_maps = {m: synth.synth_map(1000 + m, side, side, 10, None, None) for m in range(n_maps)}
+    queries = make_queries(n_maps, per_map, side, maps=all_maps)
     mine = [q for q in queries if q[0] % world == rank]  # whole maps per rank: a map is generated once per lane
     results = {}
     stacked = os.environ.get("TASI_BATCH_MODE", "stacked") == "stacked"
     chunk = int(os.environ.get("TASI_BATCH_CHUNK", "256"))
-    host_maps = {m: synth.synth_map(1000 + m, side, side, 10, None, None) for m in sorted({q[0] for q in mine})} \
-        if stacked else {}
+    host_maps = {m: all_maps[m] for m in sorted({q[0] for q in mine})} if stacked else {}
     for kind, name in ((_planner.FD, "FD*"), (_planner.DFM, "MS-DFM")):
         if stacked:
             sb = StackedBatch(kind, 1, local)
@@ -225,19 +233,35 @@ def bench_main(args, rank, world):
                          "queries_per_s": int(cnt[0]) / float(tm[0]),
                          "mcells_per_s": int(cnt[0]) * side * side / float(tm[0]) / 1e6,
                          "gpu_launches": int(cnt[2])}
+    config = {"workload": "cfg5", "maps": n_maps, "queries_per_map": per_map, "grid": "%dx%d" % (side, side),
+              "endpoints": "drawn from free cells (seed 42)",
+              "mode": "stacked: %d queries per multi-goal plan" % chunk if stacked else "lanes",
+              "lanes_per_gpu": lanes, "solver_ctas_per_lane": max(1, 444 // lanes),
+              "sharding": "whole maps per rank, no collective on the data path",
+              "timing": "wall clock of the whole batch: H2D of the (stacked) maps from host memory, goal "
+                        "upload, plan, one device walk per query (TASI_BATCH_WALK_STEPS, default 20 steps as the "
+                        "reference extractor) and D2H of the 64x64 hand-off window per query; max over ranks"}
+    return results, config
+
+
+def bench_main(args, rank, world):
+    import torch
+    import torch.distributed as dist
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — the product path has no CPU fallback")
+    local = int(os.environ.get("LOCAL_RANK", rank))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    side = 1024 if args.side == 4096 else args.side
+    results, config = measure(rank, world, local, side, args.full)
     if rank == 0:
         print(json.dumps({
             "metric": "Mcells/s over a batch of independent start/goal queries on %dx%d maps (FD* and MS-DFM)" % (side, side),
             "value": results["MS-DFM"]["mcells_per_s"], "unit": "Mcells/s", "n_gpus": world, "steps": 1, "warmup": 1,
             "ms_per_step": results["MS-DFM"]["seconds"] * 1e3, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "cfg5", "maps": n_maps, "queries_per_map": per_map, "grid": "%dx%d" % (side, side),
-                       "mode": "stacked: %d queries per multi-goal plan" % chunk if stacked else "lanes",
-                       "lanes_per_gpu": lanes, "solver_ctas_per_lane": max(1, 444 // lanes),
-                       "sharding": "whole maps per rank, no collective on the data path",
-                       "timing": "wall clock of the whole batch: H2D of the (stacked) maps from host memory, goal "
-                                 "upload, plan, one device walk per query (TASI_BATCH_WALK_STEPS, default 20 steps as the "
-                                 "reference extractor) and D2H of the 64x64 hand-off window per query; max over ranks"},
+            "config": config,
             "per_planner": results}), flush=True)
     if world > 1:
         dist.destroy_process_group()

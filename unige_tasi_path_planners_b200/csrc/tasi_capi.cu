@@ -178,20 +178,36 @@ solver_fn pick_solver(int kind, int mode, int strip) {
 }
 
 // (Re)allocate the device arrays for a map of `rows` x `W` cells. Margins: cost bytes 255, values INF.
+// The geometry is committed only once every allocation has succeeded: a failed cudaMalloc leaves the planner
+// without a grid (W = rows = 0, all pointers null), so a retry of set_map with the same shape allocates again
+// instead of taking the "same shape" short cut over null arrays.
+int alloc_grid_arrays(tasi_planner *p, int EY, int nt, unsigned q) {
+    CU_TRY(p, cudaMalloc(&p->g_base, sizeof(float) * p->gpitch * p->g_rows));
+    CU_TRY(p, cudaMalloc(&p->c_base, (size_t) p->cpitch * p->g_rows));
+    CU_TRY(p, cudaMalloc(&p->state, sizeof(int) * nt));
+    CU_TRY(p, cudaMalloc(&p->queue, sizeof(int) * q));
+    CU_TRY(p, cudaMalloc(&p->seed, nt));
+    CU_TRY(p, cudaMalloc(&p->key, sizeof(int) * (size_t) ((nt + 3) / 4 * 4)));
+    CU_TRY(p, cudaMalloc(&p->far, sizeof(int) * 2 * (size_t) p->far_cap));
+    CU_TRY(p, cudaMalloc(&p->stage, sizeof(float) * 2 * (size_t) EY));
+    CU_TRY(p, cudaMemsetAsync(p->c_base, 255, (size_t) p->cpitch * p->g_rows, p->stream));
+    CU_TRY(p, cudaMemsetAsync(p->state, 0, sizeof(int) * nt, p->stream));
+    CU_TRY(p, cudaMemsetAsync(p->queue, 0, sizeof(int) * q, p->stream));
+    CU_TRY(p, cudaMemsetAsync(p->seed, 0, nt, p->stream));
+    return TASI_OK;
+}
+
 int alloc_grid(tasi_planner *p, int W, int rows) {
     int EX, EY;
     if (node_based(p)) { EX = rows + 1 - (p->open_top ? 1 : 0) - (p->open_bottom ? 1 : 0); EY = W + 1; }
     else { EX = rows; EY = W; }
     if (EX <= 0 || EY <= 0) { p->err = "map too small for this band configuration"; return TASI_ERR_ARG; }
-    const bool same = p->g_base && p->W == W && p->rows == rows && p->EX == EX;
-    p->W = W; p->rows = rows; p->EX = EX; p->EY = EY;
-    if (same) return TASI_OK;
+    if (p->g_base && p->W == W && p->rows == rows && p->EX == EX) return TASI_OK;
     free_grid(p);
-    p->TX = (EX + TS - 1) / TS; p->TY = (EY + TS - 1) / TS;
-    p->gpitch = (int64_t) p->TY * TS + 2 * GMARGIN;
-    p->cpitch = (int64_t) p->TY * TS + 2 * GMARGIN;
-    p->g_rows = (int64_t) p->TX * TS + 2;
-    const int nt = p->TX * p->TY;
+    p->W = p->rows = p->EX = p->EY = p->TX = p->TY = 0;
+    p->n_tiles_alloc = 0;
+    const int TX = (EX + TS - 1) / TS, TY = (EY + TS - 1) / TS;
+    const int nt = TX * TY;
     int dev_blocks = 0;
     // A relaxation round is issue- and latency-bound inside its SM, and a mid-size grid's front never offers more
     // active tiles than SMs x a few. There ONE CTA per SM with 512 threads and 2-element strips halves the serial
@@ -200,15 +216,15 @@ int alloc_grid(tasi_planner *p, int W, int rows) {
     // TASI_STRIP=2|4; FD* 4096^2 34.1 -> 30.0 ms, 8192^2 97 -> 86 ms; MFD* 4096^2 21.5 -> 18.0 ms; MS-DFM 2048^2 8.4 -> 8.1;
     // re-measured after the in-strip Gauss-Seidel order: MFD* 8192^2 is 52.9 ms with 2-element strips, 46.4 ms with 4):
     const int strip2_upto = p->kind == TASI_FD ? 100000 : (p->kind == TASI_MFD ? 33000 : 4200);
-    p->strip = nt <= strip2_upto ? 2 : 4;
+    int strip = nt <= strip2_upto ? 2 : 4;
     if (const char *e = getenv("TASI_STRIP")) {
         const int v = atoi(e);
-        if (v == 2 || v == 4) p->strip = v;
+        if (v == 2 || v == 4) strip = v;
     }
-    const int nthreads = TS * TS / p->strip;
-    CU_TRY(p, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&dev_blocks, pick_solver(p->kind, 0, p->strip), nthreads, 0));
+    const int nthreads = TS * TS / strip;
+    CU_TRY(p, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&dev_blocks, pick_solver(p->kind, 0, strip), nthreads, 0));
     int dev_blocks1 = 0;
-    CU_TRY(p, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&dev_blocks1, pick_solver(p->kind, 1, p->strip), nthreads, 0));
+    CU_TRY(p, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&dev_blocks1, pick_solver(p->kind, 1, strip), nthreads, 0));
     if (dev_blocks1 < dev_blocks) dev_blocks = dev_blocks1;
     if (dev_blocks < 1) { p->err = "solver kernel does not fit on an SM"; return TASI_ERR_CUDA; }
     int blocks = dev_blocks * p->num_sms;
@@ -217,23 +233,23 @@ int alloc_grid(tasi_planner *p, int W, int rows) {
         if (v >= 1 && v <= dev_blocks) blocks = v * p->num_sms;
     }
     if (blocks > nt) blocks = nt;
-    p->solver_blocks = blocks;
+    // ring of the work queue: a tile is queued at most once and q_push publishes without waiting for its slot, so the
+    // ring holds 2 x max(tiles, CTAs) + 1 slots rounded up to a power of two
     unsigned q = 1;
     while (q < 2u * (unsigned) std::max(nt, blocks) + 1u) q <<= 1;
-    p->qsize = q;
-    CU_TRY(p, cudaMalloc(&p->g_base, sizeof(float) * p->gpitch * p->g_rows));
-    CU_TRY(p, cudaMalloc(&p->c_base, (size_t) p->cpitch * p->g_rows));
-    CU_TRY(p, cudaMalloc(&p->state, sizeof(int) * nt));
-    CU_TRY(p, cudaMalloc(&p->queue, sizeof(int) * q));
-    CU_TRY(p, cudaMalloc(&p->seed, nt));
+    p->gpitch = (int64_t) TY * TS + 2 * GMARGIN;
+    p->cpitch = (int64_t) TY * TS + 2 * GMARGIN;
+    p->g_rows = (int64_t) TX * TS + 2;
     p->far_cap = 2 * nt + 64;
-    CU_TRY(p, cudaMalloc(&p->key, sizeof(int) * (size_t) ((nt + 3) / 4 * 4)));
-    CU_TRY(p, cudaMalloc(&p->far, sizeof(int) * 2 * (size_t) p->far_cap));
-    CU_TRY(p, cudaMalloc(&p->stage, sizeof(float) * 2 * (size_t) EY));
-    CU_TRY(p, cudaMemsetAsync(p->c_base, 255, (size_t) p->cpitch * p->g_rows, p->stream));
-    CU_TRY(p, cudaMemsetAsync(p->state, 0, sizeof(int) * nt, p->stream));
-    CU_TRY(p, cudaMemsetAsync(p->queue, 0, sizeof(int) * q, p->stream));
-    CU_TRY(p, cudaMemsetAsync(p->seed, 0, nt, p->stream));
+    const int rc = alloc_grid_arrays(p, EY, nt, q);
+    if (rc != TASI_OK) {
+        free_grid(p);
+        return rc;
+    }
+    p->W = W; p->rows = rows; p->EX = EX; p->EY = EY; p->TX = TX; p->TY = TY;
+    p->strip = strip;
+    p->solver_blocks = blocks;
+    p->qsize = q;
     p->n_tiles_alloc = nt;
     p->initialize_search = true;  // a new geometry invalidates any previous field
     p->patch_pending = false;

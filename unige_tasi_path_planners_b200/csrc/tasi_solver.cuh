@@ -15,9 +15,11 @@
 //     under-consistent branch does lazily, FieldDPlanner_impl.h:98-112), then phase 2 re-relaxes.
 //
 // Tile states: 0 idle, DIRTY queued, RUN being processed, RUN|DIRTY halo changed while processing (the
-// same CTA reloads and continues). A tile is in the queue at most once, so a ring of >= max(tiles, CTAs)
-// slots can never overflow; poppers take tickets and wait for their slot, `pending` (queued + running
-// tiles) reaching 0 ends the kernel. A wall-clock watchdog turns any would-be hang into an error code.
+// same CTA reloads and continues). A tile is in the queue at most once, so a ring of 2 x max(tiles, CTAs) + 1
+// slots (rounded up to a power of two, alloc_grid) can never overflow and a pusher never has to wait for its
+// slot; poppers take tickets and wait for their slot, `pending` (queued + running tiles) reaching 0 ends the
+// kernel. A wall-clock watchdog on GLOBAL progress (no push anywhere for timeout_ns) turns any would-be hang
+// into an error code.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -112,8 +114,8 @@ __device__ __forceinline__ void q_fail(const GridDesc &d) {
 __device__ inline void q_push(const GridDesc &d, int tile) {
     atomicAdd(&d.ctl->pending, 1);
     unsigned long long t = atomicAdd(&d.ctl->tail, 1ULL);
-    // The ring has >= 2 x tiles slots and a tile is queued at most once, so the slot of this ticket was emptied by
-    // its previous owner long ago (CTAs are not preempted individually): publish without waiting for a reply.
+    // The ring has 2 x max(tiles, CTAs) + 1 slots and a tile is queued at most once, so the slot of this ticket was
+    // emptied by its previous owner long ago (CTAs are not preempted individually): publish without waiting for a reply.
     atomicExch(&d.queue[(unsigned) t & d.qmask], tile + 1);
 }
 
@@ -124,7 +126,7 @@ __device__ inline int q_pop(const GridDesc &d) {
     unsigned long long t = atomicAdd(&d.ctl->head, 1ULL);
     volatile int *slot = &d.queue[(unsigned) t & d.qmask];
     volatile int *done = &d.ctl->done;
-    unsigned long long t0 = 0;
+    unsigned long long t0 = 0, tail0 = 0;
     unsigned ns = 32, polls = 0;
     for (;;) {
         int v = *slot;
@@ -135,8 +137,17 @@ __device__ inline int q_pop(const GridDesc &d) {
         // the slot is this ticket's own word; `done` shares its line with the queue counters, so it is looked at
         // on every fourth poll only and the back-off can stay short (a waiting CTA sits on the critical path)
         if ((++polls & 3u) == 0 && *done) return -1;
-        if (t0 == 0) t0 = globaltimer_ns();
-        else if (globaltimer_ns() - t0 > d.ctl->timeout_ns) { q_fail(d); return -1; }
+        if (t0 == 0) {
+            t0 = globaltimer_ns();
+            tail0 = *(volatile unsigned long long *) &d.ctl->tail;
+        } else if (globaltimer_ns() - t0 > d.ctl->timeout_ns) {
+            // the watchdog fires on lack of GLOBAL progress: if anything was pushed since this wait began (other CTAs
+            // are working; or the device is shared and some CTAs of this launch were not resident yet), wait on
+            const unsigned long long tl = *(volatile unsigned long long *) &d.ctl->tail;
+            if (tl == tail0) { q_fail(d); return -1; }
+            tail0 = tl;
+            t0 = globaltimer_ns();
+        }
         __nanosleep(ns);
         if (ns < Q_SLEEP_MAX_NS) ns <<= 1;
     }
@@ -699,18 +710,26 @@ __global__ void seed_goal_kernel(GridDesc d) {
 }
 
 // Move the tiles flagged in seed[] into the work queue (runs alone, before the solver).
-// One warp per flagged tile: its key becomes (at most) the lowest value it holds, so that seeded tiles enter the
-// value-ordered schedule where they belong instead of all running at once with stale inputs (a replan seeds
-// thousands of tiles; the ones nearer the goal must settle first).
+// One warp per flagged tile: its key becomes (at most) the lowest value it can READ — the 34x34 window of the tile
+// plus its one-element halo ring — so that seeded tiles enter the value-ordered schedule where they belong instead
+// of all running at once with stale inputs (a replan seeds thousands of tiles; the ones nearer the goal must settle
+// first). The halo ring matters: a key has to be a lower bound on anything the visit can write (the focus test of
+// advance_threshold and the band limit rely on it), and after a cost-lowering patch a tile whose interior is all
+// INF (a block of believed obstacles that opened up) takes its new values from its halo.
 __global__ void seed_keys_kernel(GridDesc d) {
     const int n = d.TX * d.TY, lane = threadIdx.x & 31;
     const int nwarps = (gridDim.x * blockDim.x) >> 5;
     for (int t = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; t < n; t += nwarps) {
         if (!d.seed[t]) continue;
         const int tx = t / d.TY, ty = t - tx * d.TY;
-        const float *base = d.g + (int64_t) (tx * TS) * d.gpitch + ty * TS + lane;
+        // rows -1..32 of the window exist for every tile (margin / halo rows), columns -1 and 32 too (GMARGIN)
+        const float *base = d.g + (int64_t) (tx * TS - 1) * d.gpitch + ty * TS;
         int m = INF_BITS;
-        for (int r = 0; r < TS; ++r) m = min(m, __float_as_int(__ldcg(base + (int64_t) r * d.gpitch)));  // values >= 0
+        for (int r = 0; r < TS + 2; ++r) {
+            const float *rp = base + (int64_t) r * d.gpitch;
+            m = min(m, __float_as_int(__ldcg(rp + lane)));  // values >= 0: int order == float order
+            if (lane < 2) m = min(m, __float_as_int(__ldcg(rp + (lane ? TS : -1))));
+        }
         m = __reduce_min_sync(0xffffffffu, m);
         if (lane == 0) atomicMin(&d.key[t], m);
     }

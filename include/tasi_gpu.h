@@ -146,7 +146,50 @@ int tasi_set_solver_blocks(tasi_planner *p, int max_blocks);
 int tasi_get_stats(tasi_planner *p, tasi_stats *out);
 const char *tasi_last_error(tasi_planner *p);
 
-/* ---- row-band sharding (one band per GPU; halo rows are exchanged by the caller, e.g. NCCL send/recv) ----
+/* ---- sharded planner: one grid over several GPUs behind the same entry points ----
+ * The reference has no multi-device path; ReplannerBase's surface (ReplannerBase.h:39-123) stays what the caller sees:
+ * the handle returned here takes tasi_set_map / tasi_patch_map / tasi_set_start / tasi_set_goal / tasi_step /
+ * tasi_read_window / tasi_read_field / tasi_extract_paths / tasi_get_stats exactly as a single-device handle does, and
+ * the converged field is bit-identical to the single-device field. The element rows are cut into bands dealt out
+ * cyclically over the devices; every device runs ONE persistent solver over the stack of its bands, boundary rows are
+ * exchanged and the common value limit raised on the device streams (csrc/tasi_shard.cuh).
+ *
+ * tasi_create_sharded: all devices driven by this process (one stream per device, peer-mapped exchange;
+ * TASI_SHARD_NCCL=1 or missing peer access: NCCL via ncclCommInitAll). device_ids may repeat a device (several ranks
+ * on one GPU: the single-GPU test of the protocol).
+ * tasi_create_sharded_rank: one rank per process, e.g. one per GPU under torchrun; rank 0 obtains 128 bytes from
+ * tasi_nccl_unique_id and the caller hands them to every rank (broadcast); halo rows then travel by ncclSend/ncclRecv
+ * and the convergence quantities by ncclAllReduce on the planner's stream. Every rank must make the same calls in the
+ * same order (set_map with the WHOLE map, patch_map, step ...); tasi_read_window / tasi_extract_paths only reach rows
+ * this rank owns, tasi_field_checksum covers the whole field.
+ * Not available on a sharded handle (TASI_ERR_STATE): set_map_device, set_map_stack, set_goals, set_focus,
+ * read_parents, field_device / cost_device, the tasi_band_* primitives. */
+int tasi_create_sharded(int kind, int level, const int *device_ids, int n_dev, tasi_planner **out);
+int tasi_nccl_unique_id(void *out128);
+int tasi_create_sharded_rank(int kind, int level, int device, int rank, int n_ranks, const void *nccl_unique_id,
+                             tasi_planner **out);
+/* Bands per device (default 4, TASI_BANDS_PER_GPU) and threshold widths of the tile schedule between two exchanges
+ * (default 2, TASI_BAND_PHASES); values < 1 keep the current setting. Before set_map. */
+int tasi_shard_config(tasi_planner *p, int bands_per_device, int phases_per_exchange);
+
+typedef struct tasi_shard_stats {
+    int32_t n_ranks, bands, bands_per_rank, rows_per_band;
+    int32_t nccl;               /* 1: NCCL send/recv + all-reduce, 0: peer-mapped reads (ranks of one process) */
+    int32_t pad;
+    uint64_t exchanges;         /* outer iterations of the relax loop (incl. the few empty ones queued past convergence) */
+    uint64_t inval_exchanges;   /* outer iterations of the invalidate loop of a replan */
+    float wall_ms;              /* host wall clock of the step */
+    float solver_ms_max_rank;   /* time inside the persistent solver launches, busiest and idlest rank: */
+    float solver_ms_min_rank;   /* solver_ms_max_rank / wall_ms is the share of the step spent solving */
+} tasi_shard_stats;
+int tasi_shard_get_stats(tasi_planner *p, tasi_shard_stats *out);
+
+/* Order-independent 64-bit checksum of the value field (sum over the elements of a mix of global index and value bits):
+ * equal for a sharded and a single-device planner iff their fields are bit-identical. On a multi-process sharded handle
+ * it is collective (every rank calls it and gets the sum over the whole field). */
+int tasi_field_checksum(tasi_planner *p, uint64_t *sum);
+
+/* ---- row-band primitives (one band per handle; the building blocks the sharded planner grew out of; halo rows are exchanged by the caller, e.g. NCCL send/recv) ----
  * A band holds element rows [0,ex) of its own plus one halo row above (row -1) and below (row ex) in the
  * same device array. tasi_band_config marks which sides are open (have a neighbour band) and gives the
  * band's first global element row so start/goal can be given in global coordinates. The band's map must

@@ -5,4 +5,4 @@ reference's planner interface on top of it. Importing the package does not load 
 planner does, and raises if it (or a CUDA device) is missing.
 """
 from .planner import (DFM, FD, MFD, DFMPlanner, FieldDPlanner, FieldView, GpuPlanner, ShiftedGridPlanner,  # noqa: F401
-                      TasiError, PLANNERS, LOOP_OK, LOOP_FAILURE_NO_GRAPH, LOOP_FAILURE_NO_GOAL)
+                      ShardedPlanner, TasiError, PLANNERS, LOOP_OK, LOOP_FAILURE_NO_GRAPH, LOOP_FAILURE_NO_GOAL)

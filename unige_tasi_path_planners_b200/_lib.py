@@ -42,6 +42,15 @@ class Stats(C.Structure):
         return {n: getattr(self, n) for n, _ in self._fields_}
 
 
+class ShardStats(C.Structure):
+    _fields_ = [("n_ranks", C.c_int32), ("bands", C.c_int32), ("bands_per_rank", C.c_int32), ("rows_per_band", C.c_int32),
+                ("nccl", C.c_int32), ("pad", C.c_int32), ("exchanges", C.c_uint64), ("inval_exchanges", C.c_uint64),
+                ("wall_ms", C.c_float), ("solver_ms_max_rank", C.c_float), ("solver_ms_min_rank", C.c_float)]
+
+    def as_dict(self):
+        return {n: getattr(self, n) for n, _ in self._fields_ if n != "pad"}
+
+
 # every symbol include/tasi_gpu.h declares: name -> (restype, argtypes)
 SIGNATURES = {
     "tasi_create": (C.c_int, [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_void_p)]),
@@ -77,6 +86,12 @@ SIGNATURES = {
     "tasi_read_parents": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),
     "tasi_set_map_stack": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.c_int, _i32p, C.c_int, C.c_int, C.c_int]),
     "tasi_set_focus": (C.c_int, [C.c_void_p, C.c_int, C.c_float]),
+    "tasi_create_sharded": (C.c_int, [C.c_int, C.c_int, _i32p, C.c_int, C.POINTER(C.c_void_p)]),
+    "tasi_nccl_unique_id": (C.c_int, [C.c_void_p]),
+    "tasi_create_sharded_rank": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.POINTER(C.c_void_p)]),
+    "tasi_shard_config": (C.c_int, [C.c_void_p, C.c_int, C.c_int]),
+    "tasi_shard_get_stats": (C.c_int, [C.c_void_p, C.POINTER(ShardStats)]),
+    "tasi_field_checksum": (C.c_int, [C.c_void_p, _u64p]),
     "tasi_extract_paths": (C.c_int, [C.c_void_p, _f32p, _f32p, _i32p, C.c_int, C.c_int, C.c_int, C.c_int, _f32p, C.c_int,
                                      _i32p, _f32p, C.c_int, _i32p, _f32p, _i32p, _f32p]),
 }

@@ -19,7 +19,11 @@
 
 using namespace tasi;
 
+struct tasi_shard;
+
 struct tasi_planner {
+    tasi_shard *shard = nullptr;  // set on the handle of a sharded planner (tasi_shard.cuh): every entry point forwards
+    int band_rt = 0;              // > 0: this grid is a stack of row bands of band_rt tile rows (a member of a shard)
     int kind = TASI_FD, level = 0, device = 0;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, evs0 = nullptr, evs1 = nullptr;
@@ -139,7 +143,8 @@ GridDesc make_desc(const tasi_planner *p) {
     d.inval_tol = (p->kind == TASI_DFM) ? 1e-6f : 0.0f;
     d.n_focus = 0;
     d.focus_slack = p->focus_slack;
-    if (p->focus && !p->open_top && !p->open_bottom) {
+    d.band_rt = p->band_rt;
+    if (p->focus && !p->open_top && !p->open_bottom && p->band_rt == 0) {
         // Graph::set_start: start_cell_ = Cell(start) rounds (Cell.cpp:20-21); FD*/MFD* wait for the cell's four
         // corner nodes (FieldDPlanner_impl.h:12, Cell.cpp:58-60), MS-DFM for the cell itself
         const int cx = (int) roundf(p->start_x), cy = (int) roundf(p->start_y);
@@ -197,12 +202,19 @@ int alloc_grid_arrays(tasi_planner *p, int EY, int nt, unsigned q) {
     return TASI_OK;
 }
 
+int alloc_grid_dims(tasi_planner *p, int W, int rows, int EX, int EY);
+
 int alloc_grid(tasi_planner *p, int W, int rows) {
     int EX, EY;
     if (node_based(p)) { EX = rows + 1 - (p->open_top ? 1 : 0) - (p->open_bottom ? 1 : 0); EY = W + 1; }
     else { EX = rows; EY = W; }
+    return alloc_grid_dims(p, W, rows, EX, EY);
+}
+
+// `rows` cell rows stored, EX x EY elements (a band stack of a sharded planner passes its own extents)
+int alloc_grid_dims(tasi_planner *p, int W, int rows, int EX, int EY) {
     if (EX <= 0 || EY <= 0) { p->err = "map too small for this band configuration"; return TASI_ERR_ARG; }
-    if (p->g_base && p->W == W && p->rows == rows && p->EX == EX) return TASI_OK;
+    if (p->g_base && p->W == W && p->rows == rows && p->EX == EX && p->EY == EY) return TASI_OK;
     free_grid(p);
     p->W = p->rows = p->EX = p->EY = p->TX = p->TY = 0;
     p->n_tiles_alloc = 0;
@@ -377,6 +389,8 @@ int init_field(tasi_planner *p) {
 
 }  // namespace
 
+#include "tasi_shard.cuh"
+
 extern "C" {
 
 int tasi_create(int kind, int level, int device, tasi_planner **out) {
@@ -414,6 +428,11 @@ int tasi_create(int kind, int level, int device, tasi_planner **out) {
 
 int tasi_destroy(tasi_planner *p) {
     if (!p) return TASI_OK;
+    if (p->shard) {
+        shard_destroy(p->shard);
+        delete p;
+        return TASI_OK;
+    }
     cudaSetDevice(p->device);
     if (p->stream) cudaStreamSynchronize(p->stream);
     free_grid(p);
@@ -429,6 +448,7 @@ int tasi_destroy(tasi_planner *p) {
 
 int tasi_reset(tasi_planner *p) {
     if (!p) return TASI_ERR_ARG;
+    if (p->shard) p->shard->initialize_search = true;
     p->initialize_search = true;
     return TASI_OK;
 }
@@ -436,11 +456,16 @@ int tasi_reset(tasi_planner *p) {
 int tasi_set_occupancy_threshold(tasi_planner *p, float t) {
     if (!p) return TASI_ERR_ARG;
     p->thr = (int) (unsigned char) (t * 255.0f);  // Graph.cpp:18-20 (member is an unsigned char)
+    if (p->shard) {
+        p->shard->thr = p->thr;
+        for (ShardMember &m : p->shard->local) m.p->thr = p->thr;
+    }
     return TASI_OK;
 }
 
 int tasi_set_heuristic_multiplier(tasi_planner *p, float mult) {
     if (!p) return TASI_ERR_ARG;
+    if (p->shard) p->shard->heuristic_multiplier = mult;
     p->heuristic_multiplier = mult;
     return TASI_OK;
 }
@@ -462,16 +487,19 @@ static int set_map_common(tasi_planner *p, const uint8_t *src, int width, int le
 }
 
 int tasi_set_map(tasi_planner *p, const uint8_t *host_map, int width, int length) {
+    if (p && p->shard) return shard_set_map(p->shard, host_map, width, length);
     return set_map_common(p, host_map, width, length, width, cudaMemcpyHostToDevice);
 }
 
 int tasi_set_map_device(tasi_planner *p, const uint8_t *dev_map, int width, int length, int64_t pitch) {
+    if (p && p->shard) return sh_fail(p->shard, TASI_ERR_STATE, "set_map_device: not available on a sharded planner");
     return set_map_common(p, dev_map, width, length, pitch, cudaMemcpyDeviceToDevice);
 }
 
 int tasi_set_map_stack(tasi_planner *p, const uint8_t *const *maps, int n_maps, const int *index, int n_blocks,
                        int width, int length) {
     if (!p || !maps || !index || n_maps <= 0 || n_blocks <= 0 || width <= 0 || length <= 0) return TASI_ERR_ARG;
+    if (p->shard) return sh_fail(p->shard, TASI_ERR_STATE, "set_map_stack: not available on a sharded planner");
     if (p->open_top || p->open_bottom) return fail(p, TASI_ERR_STATE, "set_map_stack: not available on a row band");
     for (int b = 0; b < n_blocks; ++b)
         if (index[b] < 0 || index[b] >= n_maps || !maps[index[b]]) return fail(p, TASI_ERR_ARG, "set_map_stack: bad index");
@@ -504,6 +532,10 @@ int tasi_set_map_stack(tasi_planner *p, const uint8_t *const *maps, int n_maps, 
 int tasi_synth_map(tasi_planner *p, uint64_t seed, int width, int length, int64_t row0, int p_obs, int sx, int sy,
                    int gx, int gy) {
     if (!p || width <= 0 || length <= 0) return TASI_ERR_ARG;
+    if (p->shard) {
+        if (row0 != 0) return sh_fail(p->shard, TASI_ERR_ARG, "synth_map: a sharded planner generates the whole map (row0 = 0)");
+        return shard_synth_map(p->shard, seed, width, length, p_obs, sx, sy, gx, gy);
+    }
     CU_TRY(p, cudaSetDevice(p->device));
     int rc = alloc_grid(p, width, length);
     if (rc != TASI_OK) return rc;
@@ -518,6 +550,7 @@ int tasi_synth_map(tasi_planner *p, uint64_t seed, int width, int length, int64_
 }
 
 int tasi_read_map(tasi_planner *p, uint8_t *host_out) {
+    if (p && p->shard) return shard_read_map(p->shard, host_out);
     if (!p || !host_out || p->initialize_graph) return TASI_ERR_ARG;
     CU_TRY(p, cudaSetDevice(p->device));
     const int dst_row0 = (node_based(p) && p->open_top) ? -1 : 0;
@@ -528,6 +561,7 @@ int tasi_read_map(tasi_planner *p, uint8_t *host_out) {
 }
 
 int tasi_patch_map(tasi_planner *p, const uint8_t *host_patch, int x, int y, int w, int h, uint64_t *n_changed) {
+    if (p && p->shard) return shard_patch_map(p->shard, host_patch, x, y, w, h, n_changed);
     if (!p || !host_patch || p->initialize_graph) return TASI_ERR_ARG;
     if (x < 0 || y < 0 || w <= 0 || h <= 0 || (int64_t) x + h > p->rows || (int64_t) y + w > p->W) {
         p->err = "patch outside the map";  // the reference asserts (Graph.cpp:38-41)
@@ -547,11 +581,11 @@ int tasi_patch_map(tasi_planner *p, const uint8_t *host_patch, int x, int y, int
     CU_TRY(p, cudaMemsetAsync(&p->ctl->n_changed, 0, sizeof(unsigned long long), p->stream));
     GridDesc d = make_desc(p);
     const int blocks = (int) std::min<size_t>((n + 255) / 256, (size_t) p->num_sms * 16);
-    patch_apply_kernel<<<blocks, 256, 0, p->stream>>>(d, p->patch_buf, p->chg_buf, x, y, w, h);
+    patch_apply_kernel<<<blocks, 256, 0, p->stream>>>(d, p->patch_buf, p->chg_buf, x, y, w, h, 0, p->rows);
     switch (p->kind) {
-        case TASI_FD: patch_seed_kernel<TASI_KIND_FD><<<blocks, 256, 0, p->stream>>>(d, p->chg_buf, x, y, w, h); break;
-        case TASI_DFM: patch_seed_kernel<TASI_KIND_DFM><<<blocks, 256, 0, p->stream>>>(d, p->chg_buf, x, y, w, h); break;
-        default: patch_seed_kernel<TASI_KIND_MFD><<<blocks, 256, 0, p->stream>>>(d, p->chg_buf, x, y, w, h); break;
+        case TASI_FD: patch_seed_kernel<TASI_KIND_FD><<<blocks, 256, 0, p->stream>>>(d, p->chg_buf, x, y, w, h, 0, p->EX); break;
+        case TASI_DFM: patch_seed_kernel<TASI_KIND_DFM><<<blocks, 256, 0, p->stream>>>(d, p->chg_buf, x, y, w, h, 0, p->EX); break;
+        default: patch_seed_kernel<TASI_KIND_MFD><<<blocks, 256, 0, p->stream>>>(d, p->chg_buf, x, y, w, h, 0, p->EX); break;
     }
     CU_TRY(p, cudaGetLastError());
     DevCtl hc;
@@ -569,6 +603,10 @@ static void round_elem(float x, float y, int64_t *ex, int64_t *ey) {
 
 int tasi_set_start(tasi_planner *p, float x, float y) {
     if (!p) return TASI_ERR_ARG;
+    if (p->shard) {
+        p->shard->start_x = x; p->shard->start_y = y;
+        p->shard->new_start = true;
+    }
     p->start_x = x; p->start_y = y;
     p->new_start = true;
     return TASI_OK;
@@ -583,11 +621,18 @@ int tasi_set_goal(tasi_planner *p, float x, float y) {
     p->goal_x = x; p->goal_y = y; p->goal_ex = ex; p->goal_ey = ey;
     p->have_goal_elem = true;
     p->goal_set = true;
+    if (tasi_shard *s = p->shard) {
+        s->new_goal = p->new_goal;
+        s->goal_x = x; s->goal_y = y; s->goal_ex = ex; s->goal_ey = ey;
+        s->have_goal_elem = true;
+        s->goal_set = true;
+    }
     return TASI_OK;
 }
 
 int tasi_set_goals(tasi_planner *p, const float *xy, int n) {
     if (!p || !xy || n < 1) return TASI_ERR_ARG;
+    if (p->shard) return sh_fail(p->shard, TASI_ERR_STATE, "set_goals: not available on a sharded planner");
     CU_TRY(p, cudaSetDevice(p->device));
     int rc = tasi_set_goal(p, xy[0], xy[1]);
     if (rc != TASI_OK) return rc;
@@ -616,6 +661,11 @@ int tasi_set_goals(tasi_planner *p, const float *xy, int n) {
 
 int tasi_step(tasi_planner *p, float *u_ms, float *p_ms, uint64_t *n_updated, uint64_t *n_expanded) {
     if (!p) return TASI_ERR_ARG;
+    if (p->shard) {
+        const int rc = shard_step(p->shard, u_ms, p_ms, n_updated, n_expanded);
+        p->new_goal = false;
+        return rc;
+    }
     if (p->initialize_graph) return TASI_LOOP_FAILURE_NO_GRAPH;  // ReplannerBase.h:44
     if (!p->goal_set) return TASI_LOOP_FAILURE_NO_GOAL;         // ReplannerBase.h:45
     CU_TRY(p, cudaSetDevice(p->device));
@@ -690,6 +740,12 @@ int tasi_step(tasi_planner *p, float *u_ms, float *p_ms, uint64_t *n_updated, ui
 }
 
 int tasi_field_dims(tasi_planner *p, int *ex, int *ey) {
+    if (p && p->shard) {
+        if (p->shard->initialize_graph) return TASI_ERR_ARG;
+        if (ex) *ex = (int) p->shard->n_elem_rows;
+        if (ey) *ey = p->shard->EY;
+        return TASI_OK;
+    }
     if (!p || p->initialize_graph) return TASI_ERR_ARG;
     if (ex) *ex = p->EX;
     if (ey) *ey = p->EY;
@@ -697,6 +753,7 @@ int tasi_field_dims(tasi_planner *p, int *ex, int *ey) {
 }
 
 int tasi_read_window(tasi_planner *p, int x0, int y0, int nx, int ny, float *host_out) {
+    if (p && p->shard) return shard_read_window(p->shard, x0, y0, nx, ny, host_out);
     if (!p || !host_out || nx <= 0 || ny <= 0 || p->initialize_graph) return TASI_ERR_ARG;
     CU_TRY(p, cudaSetDevice(p->device));
     const int xa = std::max(x0, 0), xb = std::min(x0 + nx, p->EX);
@@ -714,11 +771,16 @@ int tasi_read_window(tasi_planner *p, int x0, int y0, int nx, int ny, float *hos
 }
 
 int tasi_read_field(tasi_planner *p, float *host_out) {
+    if (p && p->shard) {
+        if (p->shard->initialize_graph) return TASI_ERR_ARG;
+        return shard_read_window(p->shard, 0, 0, (int) p->shard->n_elem_rows, p->shard->EY, host_out);
+    }
     if (!p || p->initialize_graph) return TASI_ERR_ARG;
     return tasi_read_window(p, 0, 0, p->EX, p->EY, host_out);
 }
 
 int tasi_field_device(tasi_planner *p, float **dev_ptr, int64_t *pitch_elems) {
+    if (p && p->shard) return sh_fail(p->shard, TASI_ERR_STATE, "field_device: a sharded field has no single device view");
     if (!p || !p->g_base) return TASI_ERR_ARG;
     if (dev_ptr) *dev_ptr = g_origin(p);
     if (pitch_elems) *pitch_elems = p->gpitch;
@@ -726,6 +788,7 @@ int tasi_field_device(tasi_planner *p, float **dev_ptr, int64_t *pitch_elems) {
 }
 
 int tasi_cost_device(tasi_planner *p, uint8_t **dev_ptr, int64_t *pitch_bytes) {
+    if (p && p->shard) return sh_fail(p->shard, TASI_ERR_STATE, "cost_device: a sharded grid has no single device view");
     if (!p || !p->c_base) return TASI_ERR_ARG;
     if (dev_ptr) *dev_ptr = c_origin(p);
     if (pitch_bytes) *pitch_bytes = p->cpitch;
@@ -734,21 +797,30 @@ int tasi_cost_device(tasi_planner *p, uint8_t **dev_ptr, int64_t *pitch_bytes) {
 
 int tasi_set_solver_blocks(tasi_planner *p, int max_blocks) {
     if (!p || max_blocks < 0) return TASI_ERR_ARG;
+    if (p->shard) p->shard->max_blocks = max_blocks;
     p->max_blocks = max_blocks;
     return TASI_OK;
 }
 
 int tasi_get_stats(tasi_planner *p, tasi_stats *out) {
     if (!p || !out) return TASI_ERR_ARG;
+    if (p->shard) {
+        *out = p->shard->stats;
+        return TASI_OK;
+    }
     *out = p->stats;
     return TASI_OK;
 }
 
-const char *tasi_last_error(tasi_planner *p) { return p ? p->err.c_str() : "null planner"; }
+const char *tasi_last_error(tasi_planner *p) {
+    if (!p) return "null planner";
+    return p->shard ? p->shard->err.c_str() : p->err.c_str();
+}
 
 // ---- row bands -------------------------------------------------------------------------------------------------
 int tasi_band_config(tasi_planner *p, int64_t global_row0, int open_top, int open_bottom) {
     if (!p) return TASI_ERR_ARG;
+    if (p && p->shard) return sh_fail(p->shard, TASI_ERR_STATE, "tasi_band_config: a sharded planner runs its bands itself");
     if (!p->initialize_graph) { p->err = "band_config must precede set_map"; return TASI_ERR_STATE; }
     p->global_row0 = global_row0;
     p->open_top = open_top != 0;
@@ -757,6 +829,7 @@ int tasi_band_config(tasi_planner *p, int64_t global_row0, int open_top, int ope
 }
 
 int tasi_band_rows(tasi_planner *p, int side, float **send_row, float **recv_stage, int64_t *count) {
+    if (p && p->shard) return sh_fail(p->shard, TASI_ERR_STATE, "tasi_band_rows: a sharded planner runs its bands itself");
     if (!p || !p->g_base || side < 0 || side > 1) return TASI_ERR_ARG;
     if (send_row) *send_row = g_origin(p) + (side == 0 ? 0 : (int64_t) (p->EX - 1) * p->gpitch);
     if (recv_stage) *recv_stage = p->stage + (size_t) side * p->EY;
@@ -765,6 +838,7 @@ int tasi_band_rows(tasi_planner *p, int side, float **send_row, float **recv_sta
 }
 
 int tasi_band_import(tasi_planner *p, int side, uint64_t *n_lowered) {
+    if (p && p->shard) return sh_fail(p->shard, TASI_ERR_STATE, "tasi_band_import: a sharded planner runs its bands itself");
     if (!p || !p->g_base || side < 0 || side > 1) return TASI_ERR_ARG;
     CU_TRY(p, cudaSetDevice(p->device));
     CU_TRY(p, cudaMemsetAsync(&p->ctl->halo_lowered, 0, sizeof(unsigned long long), p->stream));
@@ -781,6 +855,7 @@ int tasi_band_import(tasi_planner *p, int side, uint64_t *n_lowered) {
 
 int tasi_band_begin(tasi_planner *p) {
     if (!p) return TASI_ERR_ARG;
+    if (p && p->shard) return sh_fail(p->shard, TASI_ERR_STATE, "tasi_band_begin: a sharded planner runs its bands itself");
     if (p->initialize_graph) return TASI_LOOP_FAILURE_NO_GRAPH;
     if (!p->goal_set) return TASI_LOOP_FAILURE_NO_GOAL;
     CU_TRY(p, cudaSetDevice(p->device));
@@ -796,6 +871,7 @@ int tasi_band_begin(tasi_planner *p) {
 }
 
 int tasi_band_solve_until(tasi_planner *p, float limit, uint64_t *n_tile_visits, float *next_key) {
+    if (p && p->shard) return sh_fail(p->shard, TASI_ERR_STATE, "tasi_band_solve_until: a sharded planner runs its bands itself");
     if (!p || !p->g_base) return TASI_ERR_ARG;
     CU_TRY(p, cudaSetDevice(p->device));
     const uint64_t before = p->stats.tile_visits;
@@ -814,6 +890,7 @@ int tasi_band_solve(tasi_planner *p, uint64_t *n_tile_visits) {
 }
 
 int tasi_band_delta(tasi_planner *p, float *delta) {
+    if (p && p->shard) return sh_fail(p->shard, TASI_ERR_STATE, "tasi_band_delta: a sharded planner runs its bands itself");
     if (!p || !p->g_base || !delta) return TASI_ERR_ARG;
     CU_TRY(p, cudaSetDevice(p->device));
     int rc = ensure_cost_stats(p);
@@ -822,29 +899,24 @@ int tasi_band_delta(tasi_planner *p, float *delta) {
     return TASI_OK;
 }
 
-int tasi_extract_paths(tasi_planner *p, const float *starts_xy, const float *goals_xy, const int *row_ranges, int n,
-                       int max_steps, int lookahead, int allow_indirect, float *xy, int cap_points, int *n_points,
-                       float *step_costs, int cap_costs, int *n_costs, float *totals, int *status, float *e_ms) {
-    if (!p || n <= 0 || !xy || cap_points < 1 || !n_points || !totals || !status || max_steps < 1 ||
-        (step_costs && (cap_costs < 1 || !n_costs)) || ((!starts_xy || !goals_xy) && n != 1))
-        return TASI_ERR_ARG;
-    if (p->initialize_graph || p->initialize_search) return fail(p, TASI_ERR_STATE, "extract_paths: no plan yet");
-    if (p->open_top || p->open_bottom) return fail(p, TASI_ERR_STATE, "extract_paths: not available on a row band");
-    CU_TRY(p, cudaSetDevice(p->device));
-    const double t0 = now_ms();
+// The walks of tasi_extract_paths over the field view `v` (L x W cells), on planner p's stream with p's staging block.
+static int run_walks(tasi_planner *p, const FieldView &v, float def_sx, float def_sy, float def_gx, float def_gy,
+                     const float *starts_xy, const float *goals_xy, const int *row_ranges, int n, int max_steps,
+                     int lookahead, int allow_indirect, float *xy, int cap_points, int *n_points, float *step_costs,
+                     int cap_costs, int *n_costs, float *totals, int *status) {
     std::vector<PathQuery> q((size_t) n);
     for (int i = 0; i < n; ++i) {
-        q[i].sx = starts_xy ? starts_xy[2 * i] : p->start_x;
-        q[i].sy = starts_xy ? starts_xy[2 * i + 1] : p->start_y;
-        q[i].gx = goals_xy ? goals_xy[2 * i] : p->goal_x;
-        q[i].gy = goals_xy ? goals_xy[2 * i + 1] : p->goal_y;
+        q[i].sx = starts_xy ? starts_xy[2 * i] : def_sx;
+        q[i].sy = starts_xy ? starts_xy[2 * i + 1] : def_sy;
+        q[i].gx = goals_xy ? goals_xy[2 * i] : def_gx;
+        q[i].gy = goals_xy ? goals_xy[2 * i + 1] : def_gy;
         q[i].row0 = row_ranges ? row_ranges[2 * i] : 0;
         q[i].rows = row_ranges ? row_ranges[2 * i + 1] : 0;
-        if (row_ranges && (q[i].row0 < 0 || q[i].rows < 1 || q[i].row0 + q[i].rows > p->rows))
+        if (row_ranges && (q[i].row0 < 0 || q[i].rows < 1 || q[i].row0 + q[i].rows > v.L))
             return fail(p, TASI_ERR_ARG, "extract_paths: row range outside the map");
-        const int rows = row_ranges ? q[i].rows : p->rows;
+        const int rows = row_ranges ? q[i].rows : v.L;
         // a walk starts inside the map (Graph::is_valid(Position), Graph.cpp:57-59)
-        if (!(q[i].sx >= 0.0f && q[i].sy >= 0.0f && q[i].sx <= (float) rows && q[i].sy <= (float) p->W))
+        if (!(q[i].sx >= 0.0f && q[i].sy >= 0.0f && q[i].sx <= (float) rows && q[i].sy <= (float) v.W))
             return fail(p, TASI_ERR_ARG, "extract_paths: start outside the map");
     }
     // one device block: queries | n_points, n_costs, status | totals | xy | piece costs; everything after the
@@ -866,7 +938,6 @@ int tasi_extract_paths(tasi_planner *p, const float *starts_xy, const float *goa
         memcpy(hb, q.data(), sizeof(PathQuery) * n);
         CU_TRY(p, cudaMemcpyAsync(b, hb, sizeof(PathQuery) * n, cudaMemcpyHostToDevice, p->stream));
     }
-    FieldView v = {g_origin(p), p->gpitch, c_origin(p), p->cpitch, p->rows, p->W, p->thr, p->kind == TASI_DFM};
     int *ints = (int *) (b + o_int);
     const int warps_per_block = 4;
     extract_paths_kernel<<<(n + warps_per_block - 1) / warps_per_block, 32 * warps_per_block, 0, p->stream>>>(
@@ -883,18 +954,46 @@ int tasi_extract_paths(tasi_planner *p, const float *starts_xy, const float *goa
     memcpy(totals, hb + o_tot, sizeof(float) * 2 * n);
     memcpy(xy, hb + o_xy, sizeof(float) * 2 * cap_points * n);
     if (step_costs) memcpy(step_costs, hb + o_sc, sizeof(float) * capc * n);
-    if (e_ms) *e_ms = (float) (now_ms() - t0);
     return TASI_OK;
+}
+
+static bool walk_args_ok(int n, const float *starts_xy, const float *goals_xy, int max_steps, float *xy, int cap_points,
+                         int *n_points, float *step_costs, int cap_costs, int *n_costs, float *totals, int *status) {
+    return !(n <= 0 || !xy || cap_points < 1 || !n_points || !totals || !status || max_steps < 1 ||
+             (step_costs && (cap_costs < 1 || !n_costs)) || ((!starts_xy || !goals_xy) && n != 1));
+}
+
+int tasi_extract_paths(tasi_planner *p, const float *starts_xy, const float *goals_xy, const int *row_ranges, int n,
+                       int max_steps, int lookahead, int allow_indirect, float *xy, int cap_points, int *n_points,
+                       float *step_costs, int cap_costs, int *n_costs, float *totals, int *status, float *e_ms) {
+    if (!p || !walk_args_ok(n, starts_xy, goals_xy, max_steps, xy, cap_points, n_points, step_costs, cap_costs, n_costs,
+                            totals, status))
+        return TASI_ERR_ARG;
+    if (p->shard)
+        return shard_extract_paths(p->shard, starts_xy, goals_xy, row_ranges, n, max_steps, lookahead, allow_indirect, xy,
+                                   cap_points, n_points, step_costs, cap_costs, n_costs, totals, status, e_ms);
+    if (p->initialize_graph || p->initialize_search) return fail(p, TASI_ERR_STATE, "extract_paths: no plan yet");
+    if (p->open_top || p->open_bottom) return fail(p, TASI_ERR_STATE, "extract_paths: not available on a row band");
+    CU_TRY(p, cudaSetDevice(p->device));
+    const double t0 = now_ms();
+    FieldView v = {g_origin(p), p->gpitch, c_origin(p), p->cpitch, p->rows, p->W, p->thr, p->kind == TASI_DFM};
+    const int rc = run_walks(p, v, p->start_x, p->start_y, p->goal_x, p->goal_y, starts_xy, goals_xy, row_ranges, n,
+                             max_steps, lookahead, allow_indirect, xy, cap_points, n_points, step_costs, cap_costs, n_costs,
+                             totals, status);
+    if (e_ms) *e_ms = (float) (now_ms() - t0);
+    return rc;
 }
 
 int tasi_set_focus(tasi_planner *p, int enabled, float slack) {
     if (!p) return TASI_ERR_ARG;
+    if (p->shard && enabled) return sh_fail(p->shard, TASI_ERR_STATE, "set_focus: not available on a sharded planner");
     p->focus = enabled != 0;
     p->focus_slack = slack >= 0.0f ? slack : 4.0f * 254.0f;
     return TASI_OK;
 }
 
 int tasi_read_parents(tasi_planner *p, int x0, int y0, int nx, int ny, signed char *out) {
+    if (p && p->shard) return sh_fail(p->shard, TASI_ERR_STATE, "read_parents: not available on a sharded planner");
     if (!p || !out || nx <= 0 || ny <= 0 || p->initialize_graph) return TASI_ERR_ARG;
     if (x0 < 0 || y0 < 0 || x0 + nx > p->EX || y0 + ny > p->EY) return fail(p, TASI_ERR_ARG, "read_parents: window outside the field");
     if (p->initialize_search) return fail(p, TASI_ERR_STATE, "read_parents: no plan yet");
@@ -920,6 +1019,216 @@ int tasi_read_parents(tasi_planner *p, int x0, int y0, int nx, int ny, signed ch
     CU_TRY(p, cudaGetLastError());
     CU_TRY(p, cudaMemcpyAsync(out, dev, bytes, cudaMemcpyDeviceToHost, p->stream));
     CU_TRY(p, cudaStreamSynchronize(p->stream));
+    return TASI_OK;
+}
+
+
+}  // extern "C"
+
+// ---- sharded planner (tasi_shard.cuh) -------------------------------------------------------------------------------
+namespace {
+
+int shard_extract_paths(tasi_shard *s, const float *starts_xy, const float *goals_xy, const int *row_ranges, int n,
+                        int max_steps, int lookahead, int allow_indirect, float *xy, int cap_points, int *n_points,
+                        float *step_costs, int cap_costs, int *n_costs, float *totals, int *status, float *e_ms) {
+    if (s->initialize_graph || s->initialize_search) return sh_fail(s, TASI_ERR_STATE, "extract_paths: no plan yet");
+    if (row_ranges) return sh_fail(s, TASI_ERR_STATE, "extract_paths: row ranges are for map stacks, not for a sharded grid");
+    const double t0 = now_ms();
+    ShardMember &m0 = s->local[0];
+    tasi_planner *p = m0.p;
+    const int reach = 3 * max_steps + 8;  // a step crosses at most a few cell edges
+    for (int i = 0; i < n; ++i) {
+        const float sx = starts_xy ? starts_xy[2 * i] : s->start_x, sy = starts_xy ? starts_xy[2 * i + 1] : s->start_y;
+        const float gx = goals_xy ? goals_xy[2 * i] : s->goal_x, gy = goals_xy ? goals_xy[2 * i + 1] : s->goal_y;
+        const int64_t lo = std::max<int64_t>((int64_t) floorf(sx) - reach, 0);
+        const int64_t hi = std::min<int64_t>((int64_t) ceilf(sx) + reach + 1, s->n_elem_rows);
+        const int64_t clo = std::max<int64_t>(lo - 1, 0), chi = std::min<int64_t>(hi, s->L);
+        if (hi <= lo) return sh_fail(s, TASI_ERR_ARG, "extract_paths: start outside the map");
+        // window of value rows [lo, hi) and cost rows [clo, chi) on the first local device
+        SH_TRY(s, cudaSetDevice(m0.device));
+        const int64_t gp = (s->EY + 3) / 4 * 4, cp = (s->W + 15) / 16 * 16;
+        float *gw = nullptr;
+        uint8_t *cw = nullptr;
+        SH_TRY(s, cudaMalloc(&gw, sizeof(float) * gp * (hi - lo)));
+        if (cudaMalloc(&cw, (size_t) cp * std::max<int64_t>(chi - clo, 1)) != cudaSuccess) {
+            cudaFree(gw);
+            return sh_fail(s, TASI_ERR_CUDA, "extract_paths: out of device memory for the walk window");
+        }
+        int64_t missing = 0;
+        int rc = shard_gather_rows(s, lo, hi - lo, 0, s->EY, gw, gp, cudaMemcpyDefault, &missing);
+        int64_t have_c = 0;
+        if (rc == TASI_OK)
+            for (ShardMember &m : s->local) {
+                cudaSetDevice(m.device);
+                for (int g : m.bands) {
+                    const ShardBand &b = s->bands[g];
+                    const int64_t a0 = std::max(b.a, clo), a1 = std::min(std::min<int64_t>(b.b, s->L), chi);
+                    if (a1 <= a0) continue;
+                    if (cudaMemcpy2DAsync(cw + (a0 - clo) * cp, cp, c_origin(m.p) + (int64_t) (b.row0 + (a0 - b.a)) * m.p->cpitch,
+                                          m.p->cpitch, s->W, a1 - a0, cudaMemcpyDefault, m.p->stream) != cudaSuccess)
+                        rc = TASI_ERR_CUDA;
+                    have_c += a1 - a0;
+                }
+            }
+        if (rc == TASI_OK) rc = shard_sync_all(s);
+        if (rc == TASI_OK && (missing || have_c != chi - clo))
+            rc = sh_fail(s, TASI_ERR_STATE, "extract_paths: the rows around the start are owned by another process");
+        if (rc == TASI_OK) {
+            cudaSetDevice(m0.device);
+            // the view's origin is element (0,0) of the WHOLE grid: only rows [lo, hi) of it are backed by memory
+            FieldView v = {gw - lo * gp, gp, cw - clo * cp, cp, s->L, s->W, s->thr, s->kind == TASI_DFM};
+            const float st[2] = {sx, sy}, gl[2] = {gx, gy};
+            rc = run_walks(p, v, sx, sy, gx, gy, st, gl, nullptr, 1, max_steps, lookahead, allow_indirect,
+                           xy + (size_t) i * cap_points * 2, cap_points, n_points + i,
+                           step_costs ? step_costs + (size_t) i * cap_costs : nullptr, cap_costs, n_costs ? n_costs + i : nullptr,
+                           totals + 2 * i, status + i);
+            if (rc != TASI_OK) s->err = p->err;
+        }
+        cudaSetDevice(m0.device);
+        cudaFree(gw);
+        cudaFree(cw);
+        if (rc != TASI_OK) return rc;
+    }
+    if (e_ms) *e_ms = (float) (now_ms() - t0);
+    return TASI_OK;
+}
+
+int shard_finish_create(tasi_shard *s, int kind, int level, tasi_planner **out) {
+    tasi_planner *top = new (std::nothrow) tasi_planner();
+    if (!top) { shard_destroy(s); return TASI_ERR_ARG; }
+    top->kind = kind; top->level = level; top->device = s->local[0].device;
+    top->shard = s;
+    if (const char *e = getenv("TASI_BANDS_PER_GPU")) {
+        const int v = atoi(e);
+        if (v >= 1 && v <= 64) s->want_per_rank = v;
+    }
+    if (const char *e = getenv("TASI_BAND_PHASES")) {
+        const int v = atoi(e);
+        if (v >= 1 && v <= 64) s->k_phases = v;
+    }
+    *out = top;
+    return TASI_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int tasi_create_sharded(int kind, int level, const int *device_ids, int n_dev, tasi_planner **out) {
+    if (!out) return TASI_ERR_ARG;
+    *out = nullptr;
+    if (!device_ids || n_dev < 1 || n_dev > SHARD_MAX_RANKS || kind < TASI_FD || kind > TASI_MFD || level < 0 ||
+        level > (kind == TASI_MFD ? 2 : 1))
+        return TASI_ERR_ARG;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) return TASI_ERR_CUDA;
+    for (int i = 0; i < n_dev; ++i)
+        if (device_ids[i] < 0 || device_ids[i] >= ndev) return TASI_ERR_CUDA;
+    tasi_shard *s = new (std::nothrow) tasi_shard();
+    if (!s) return TASI_ERR_ARG;
+    s->kind = kind; s->level = level; s->world = n_dev; s->my_rank = -1;
+    s->local.resize(n_dev);
+    bool distinct = true;
+    for (int i = 0; i < n_dev; ++i) {
+        s->local[i].rank = i;
+        s->local[i].device = device_ids[i];
+        for (int j = 0; j < i; ++j) distinct = distinct && device_ids[j] != device_ids[i];
+    }
+    for (ShardMember &m : s->local)
+        if (shard_init_member(s, m) != TASI_OK) { shard_destroy(s); return TASI_ERR_CUDA; }
+    // ranks of one process read each other's buffers directly: map every pair of distinct devices
+    bool peers = true;
+    for (int i = 0; i < n_dev && peers; ++i)
+        for (int j = 0; j < n_dev && peers; ++j) {
+            if (device_ids[i] == device_ids[j]) continue;
+            int can = 0;
+            cudaDeviceCanAccessPeer(&can, device_ids[i], device_ids[j]);
+            if (!can) { peers = false; break; }
+            cudaSetDevice(device_ids[i]);
+            const cudaError_t e = cudaDeviceEnablePeerAccess(device_ids[j], 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) peers = false;
+            cudaGetLastError();
+        }
+    const char *want = getenv("TASI_SHARD_NCCL");
+    s->use_nccl = n_dev > 1 && distinct && ((want && atoi(want) != 0) || !peers);
+    if (n_dev > 1 && !peers && !distinct) { shard_destroy(s); return TASI_ERR_CUDA; }
+    if (s->use_nccl) {
+        NcclApi &N = nccl_api();
+        std::vector<ncclComm_t> comms(n_dev);
+        if (!N.load() || N.CommInitAll(comms.data(), n_dev, device_ids) != ncclSuccess) { shard_destroy(s); return TASI_ERR_CUDA; }
+        for (int i = 0; i < n_dev; ++i) s->local[i].comm = comms[i];
+    }
+    return shard_finish_create(s, kind, level, out);
+}
+
+int tasi_nccl_unique_id(void *out128) {
+    if (!out128) return TASI_ERR_ARG;
+    NcclApi &N = nccl_api();
+    if (!N.load()) return TASI_ERR_CUDA;
+    ncclUniqueId id;
+    if (N.GetUniqueId(&id) != ncclSuccess) return TASI_ERR_CUDA;
+    memcpy(out128, &id, sizeof id);
+    return TASI_OK;
+}
+
+int tasi_create_sharded_rank(int kind, int level, int device, int rank, int n_ranks, const void *nccl_unique_id,
+                             tasi_planner **out) {
+    if (!out) return TASI_ERR_ARG;
+    *out = nullptr;
+    if (n_ranks < 1 || n_ranks > SHARD_MAX_RANKS || rank < 0 || rank >= n_ranks || (n_ranks > 1 && !nccl_unique_id) ||
+        kind < TASI_FD || kind > TASI_MFD || level < 0 || level > (kind == TASI_MFD ? 2 : 1))
+        return TASI_ERR_ARG;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev) return TASI_ERR_CUDA;
+    tasi_shard *s = new (std::nothrow) tasi_shard();
+    if (!s) return TASI_ERR_ARG;
+    s->kind = kind; s->level = level; s->world = n_ranks; s->my_rank = rank;
+    s->local.resize(1);
+    s->local[0].rank = rank;
+    s->local[0].device = device;
+    if (shard_init_member(s, s->local[0]) != TASI_OK) { shard_destroy(s); return TASI_ERR_CUDA; }
+    s->use_nccl = n_ranks > 1;
+    if (s->use_nccl) {
+        NcclApi &N = nccl_api();
+        ncclUniqueId id;
+        memcpy(&id, nccl_unique_id, sizeof id);
+        cudaSetDevice(device);
+        if (!N.load() || N.CommInitRank(&s->local[0].comm, n_ranks, id, rank) != ncclSuccess) {
+            shard_destroy(s);
+            return TASI_ERR_CUDA;
+        }
+    }
+    return shard_finish_create(s, kind, level, out);
+}
+
+int tasi_shard_config(tasi_planner *p, int bands_per_device, int phases_per_exchange) {
+    if (!p || !p->shard) return TASI_ERR_ARG;
+    if (!p->shard->initialize_graph) return sh_fail(p->shard, TASI_ERR_STATE, "shard_config must precede set_map");
+    if (bands_per_device >= 1) p->shard->want_per_rank = std::min(bands_per_device, 64);
+    if (phases_per_exchange >= 1) p->shard->k_phases = std::min(phases_per_exchange, 64);
+    return TASI_OK;
+}
+
+int tasi_shard_get_stats(tasi_planner *p, tasi_shard_stats *out) {
+    if (!p || !p->shard || !out) return TASI_ERR_ARG;
+    *out = p->shard->sstats;
+    return TASI_OK;
+}
+
+int tasi_field_checksum(tasi_planner *p, uint64_t *sum) {
+    if (!p || !sum) return TASI_ERR_ARG;
+    if (p->shard) return shard_checksum(p->shard, sum);
+    if (!p->g_base || p->initialize_graph) return TASI_ERR_ARG;
+    CU_TRY(p, cudaSetDevice(p->device));
+    if (!p->cost_sum) CU_TRY(p, cudaMalloc(&p->cost_sum, 2 * sizeof(unsigned long long)));
+    unsigned long long *acc = p->cost_sum;  // scratch: the cost statistics are consumed on the host as soon as computed
+    unsigned long long h = 0;
+    CU_TRY(p, cudaMemsetAsync(acc, 0, sizeof h, p->stream));
+    field_checksum_kernel<<<p->num_sms * 4, 256, 0, p->stream>>>(g_origin(p), p->gpitch, p->EX, p->EY, p->global_row0, acc);
+    CU_TRY(p, cudaGetLastError());
+    CU_TRY(p, cudaMemcpyAsync(&h, acc, sizeof h, cudaMemcpyDeviceToHost, p->stream));
+    CU_TRY(p, cudaStreamSynchronize(p->stream));
+    *sum = h;
     return TASI_OK;
 }
 

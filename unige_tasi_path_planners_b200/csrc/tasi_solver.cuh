@@ -59,7 +59,8 @@ struct DevCtl {
     unsigned long long cyc_pop, cyc_stage, cyc_relax, cyc_post;  // SM cycles summed over CTAs (thread 0's clock)
     unsigned long long cyc_advance;  // cycles the advancing CTA spent raising the threshold (all others wait)
     int focus_hit;                  // the launch ended because the focus elements were settled (work stays parked)
-    int pad0;
+    int launches;                   // solver launches since the counters were last cleared (sharded loop)
+    unsigned long long busy_ns;     // globaltimer span of the solver launches as CTA 0 saw them, summed
     // patch bookkeeping
     unsigned long long n_changed, n_raised, n_lowered_cells, n_seed_elems;
     unsigned long long halo_lowered;
@@ -92,7 +93,15 @@ struct GridDesc {
     int n_focus;           // 0 = solve to convergence
     int2 focus[4];         // the start cell's corner nodes / the start cell, local coordinates
     float focus_slack;
+    // a stack of row bands in one grid (sharded planner, tasi_shard.cuh): every band_rt tile rows are followed by one
+    // DEAD tile row that is never scheduled; it holds the halo rows of the bands above and below it. 0 = no stack.
+    int band_rt;
 };
+
+// tile row `tx` of a band stack is a dead row (halo storage between two bands)
+__device__ __forceinline__ bool dead_tile_row(const GridDesc &d, int tx) {
+    return d.band_rt > 0 && (tx % (d.band_rt + 1)) == d.band_rt;
+}
 
 // Release/acquire fence at device scope. __threadfence() compiles to the sequentially consistent MEMBAR.SC.GPU;
 // the queue protocol only needs "my (and, after a CTA barrier, my CTA's) earlier writes are visible before my next
@@ -474,6 +483,7 @@ __global__ void __launch_bounds__(1024 / SW, SW == 4 ? 2 : 1) solver_kernel(Grid
     const int row = tid / (TS / SW), col0 = (tid % (TS / SW)) * SW;  // this thread's strip
     unsigned long long n_visits = 0, n_iters = 0, n_changed = 0, n_evals = 0;
     long long c_pop = 0, c_stage = 0, c_relax = 0, c_post = 0, c0 = clock64(), c1;
+    const unsigned long long t_launch = (blockIdx.x == 0 && tid == 0) ? globaltimer_ns() : 0ULL;
 
     // resumed band solve with nothing queued: arm_solver left one virtual pending tile for CTA 0 to retire, which
     // takes the count to 0 and starts the threshold advance
@@ -630,7 +640,8 @@ __global__ void __launch_bounds__(1024 / SW, SW == 4 ? 2 : 1) solver_kernel(Grid
                 const int seen_as = (IN_S << 0) * (tid == 0) + IN_N * (tid == 1) + IN_E * (tid == 2) + IN_W * (tid == 3) +
                                     IN_SE * (tid == 4) + IN_SW * (tid == 5) + IN_NE * (tid == 6) + IN_NW * (tid == 7);
                 const int nx = tx + dx, ny = ty + dy;
-                if (k != INF_BITS && nx >= 0 && nx < d.TX && ny >= 0 && ny < d.TY) activate(d, nx * d.TY + ny, k, seen_as);
+                if (k != INF_BITS && nx >= 0 && nx < d.TX && ny >= 0 && ny < d.TY && !dead_tile_row(d, nx))
+                    activate(d, nx * d.TY + ny, k, seen_as);
             }
             // ... while thread 32 leaves the tile (a neighbour may re-queue it at once: we no longer touch its values)
             if (tid == LEAVE_TID) {
@@ -673,6 +684,10 @@ __global__ void __launch_bounds__(1024 / SW, SW == 4 ? 2 : 1) solver_kernel(Grid
     for (int o = 16; o > 0; o >>= 1) n_evals += __shfl_down_sync(0xffffffffu, n_evals, o);
     if (lane == 0 && n_evals) atomicAdd(&d.ctl->evals, n_evals);
     if (tid == 0) {
+        if (blockIdx.x == 0) {
+            atomicAdd(&d.ctl->busy_ns, globaltimer_ns() - t_launch);
+            atomicAdd(&d.ctl->launches, 1);
+        }
         atomicAdd(&d.ctl->visits, n_visits);
         atomicAdd(&d.ctl->rounds, n_iters);
         atomicAdd(&d.ctl->cyc_pop, (unsigned long long) c_pop);
@@ -784,7 +799,10 @@ __global__ void arm_solver_kernel(GridDesc d) {
 
 // Graph::update (ProjectToolkit/Graph.cpp:36-51) on the device cost grid: rows x..x+h-1, cols y..y+w-1 take
 // the patch bytes; chg[] records which cells changed and whether the traversal cost went up (2) or down (1).
-__global__ void patch_apply_kernel(GridDesc d, const uint8_t *patch, uint8_t *chg, int x, int y, int w, int h) {
+// Changes are counted for the rows cnt_lo <= x + i < cnt_hi only (a band of a sharded grid also stores a halo copy of the
+// cell row above it, which its owner counts).
+__global__ void patch_apply_kernel(GridDesc d, const uint8_t *patch, uint8_t *chg, int x, int y, int w, int h, int cnt_lo,
+                                   int cnt_hi) {
     const int64_t n = (int64_t) w * h;
     unsigned long long c_all = 0, c_up = 0, c_dn = 0;
     for (int64_t i = blockIdx.x * (int64_t) blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x) {
@@ -797,9 +815,11 @@ __global__ void patch_apply_kernel(GridDesc d, const uint8_t *patch, uint8_t *ch
             const int oe = ov >= d.thr ? 256 : ov, ne = nv >= d.thr ? 256 : nv;
             f = ne > oe ? 2 : (ne < oe ? 1 : 3);  // 3: byte changed, cost did not
             *mv = nv;
-            ++c_all;
-            if (f == 2) ++c_up;
-            if (f == 1) ++c_dn;
+            if (x + pi >= cnt_lo && x + pi < cnt_hi) {
+                ++c_all;
+                if (f == 2) ++c_up;
+                if (f == 1) ++c_dn;
+            }
         }
         chg[i] = f;
     }
@@ -819,7 +839,8 @@ __global__ void patch_apply_kernel(GridDesc d, const uint8_t *patch, uint8_t *ch
 // (DynamicFastMarching_impl.h:106-112). Counts the distinct seeded elements (num_nodes_updated) and flags
 // their tiles. Elements of the patch range: nodes (x..x+h, y..y+w), cells (x..x+h-1, y..y+w-1).
 template <int KIND>
-__global__ void patch_seed_kernel(GridDesc d, const uint8_t *chg, int x, int y, int w, int h) {
+// Only elements of the rows seed_lo <= row < seed_hi are seeded and counted (the rows this grid owns).
+__global__ void patch_seed_kernel(GridDesc d, const uint8_t *chg, int x, int y, int w, int h, int seed_lo, int seed_hi) {
     const int ew = (KIND == TASI_KIND_DFM) ? w : w + 1, eh = (KIND == TASI_KIND_DFM) ? h : h + 1;
     const int64_t n = (int64_t) ew * eh;
     unsigned long long cnt = 0;
@@ -836,7 +857,7 @@ __global__ void patch_seed_kernel(GridDesc d, const uint8_t *chg, int x, int y, 
                     if (ci >= 0 && ci < h && cj >= 0 && cj < w && chg[(int64_t) ci * w + cj] != 0) hit = true;
                 }
         }
-        if (hit) {
+        if (hit && x + ei >= seed_lo && x + ei < seed_hi) {
             ++cnt;
             const int gx = x + ei, gy = y + ej;
             if (gx < d.EX && gy < d.EY) d.seed[(gx / TS) * d.TY + (gy / TS)] = 1;

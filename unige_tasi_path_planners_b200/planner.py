@@ -248,6 +248,13 @@ class GpuPlanner:
         self._check(self._L.tasi_read_parents(self._h, x0, y0, nx, ny, out.ctypes.data_as(C.c_void_p)))
         return out
 
+    def field_checksum(self):
+        """Order-independent 64-bit checksum of the value field (tasi_field_checksum): equal for two planners iff their
+        fields are bit-identical; on a multi-process sharded planner every rank calls it and gets the whole field's."""
+        v = C.c_uint64(0)
+        self._check(self._L.tasi_field_checksum(self._h, C.byref(v)))
+        return v.value
+
     def set_focus(self, enabled=True, slack=-1.0):
         """Plans stop once the start is settled (the reference's end_condition); later work stays parked and is
         resumed by the next step(). slack < 0 = default."""
@@ -332,3 +339,54 @@ class ShiftedGridPlanner(GpuPlanner):
 
 
 PLANNERS = {FD: FieldDPlanner, DFM: DFMPlanner, MFD: ShiftedGridPlanner}
+
+
+class ShardedPlanner(GpuPlanner):
+    """One grid over several GPUs behind the same interface (tasi_create_sharded / tasi_create_sharded_rank): the
+    planner `kind` with its element rows cut into bands dealt out cyclically over the devices. Same methods as the
+    single-device classes; the converged field is bit-identical to theirs.
+
+    devices: the devices this process drives (a device may repeat: several ranks on one GPU), or
+    rank / n_ranks / unique_id: this process is rank `rank` of `n_ranks` on `device` (one process per GPU; rank 0 gets
+    unique_id from ShardedPlanner.nccl_unique_id() and the caller broadcasts it)."""
+
+    def __init__(self, kind, level=None, devices=(0,), rank=None, n_ranks=None, unique_id=None, device=0,
+                 bands_per_device=None, phases_per_exchange=None):
+        self.kind = kind
+        self.max_level = PLANNERS[kind].max_level
+        level = self.max_level if level is None else level
+        if not (0 <= level <= self.max_level):
+            raise ValueError("optimisation level %d not defined for this planner" % level)
+        self._L = _lib.lib()
+        h = C.c_void_p()
+        if rank is None:
+            ids = np.ascontiguousarray(devices, np.int32)
+            rc = self._L.tasi_create_sharded(kind, level, ids.ctypes.data_as(C.POINTER(C.c_int32)), len(ids), C.byref(h))
+            self.device = int(ids[0])
+        else:
+            buf = C.create_string_buffer(bytes(unique_id), 128) if unique_id is not None else None
+            rc = self._L.tasi_create_sharded_rank(kind, level, device, rank, n_ranks, buf, C.byref(h))
+            self.device = device
+        if rc != _lib.OK:
+            raise TasiError(rc, "tasi_create_sharded failed (no CUDA device / NCCL? there is no CPU fallback)")
+        self._h = h
+        self.level = level
+        self.u_time = self.p_time = 0.0
+        self.num_nodes_updated = self.num_nodes_expanded = 0
+        self.heuristic_multiplier = 1.0
+        self.width = self.length = 0
+        if bands_per_device or phases_per_exchange:
+            self._check(self._L.tasi_shard_config(self._h, int(bands_per_device or 0), int(phases_per_exchange or 0)))
+
+    @staticmethod
+    def nccl_unique_id():
+        buf = C.create_string_buffer(128)
+        rc = _lib.lib().tasi_nccl_unique_id(buf)
+        if rc != _lib.OK:
+            raise TasiError(rc, "tasi_nccl_unique_id failed (libnccl.so.2 not found?)")
+        return buf.raw
+
+    def shard_stats(self):
+        s = _lib.ShardStats()
+        self._check(self._L.tasi_shard_get_stats(self._h, C.byref(s)))
+        return s.as_dict()

@@ -7,8 +7,11 @@ synthetic traversability grid with 10 % random obstacles of SURVEY.md 8(d) (seed
 (4090,4090), occupancy threshold 1.0). One step = one plan to convergence (reset + step). With N > 1 every
 rank plans its own grid of the same shape — the "independent queries, one slice per GPU" sharding of the
 north star, no data-path collective — so scaling is weak and value = N * cells / max-over-ranks time.
-`--workload bands` runs the row-band sharded single grid instead (FD*, NCCL halo exchange; N >= 2);
-`--workload cfg3` the MFD* 16384^2 plan + replan-latency measurement (1 GPU).
+The same JSON line carries the rest of BASELINE.json's metric, each measured by its own module outside cfg2's timed
+region: `replan` (cfg3: MFD* 16384^2 plan + replan latency after a 1 % patch, N = 1), `batch` (cfg5: independent queries
+on 1024^2 maps, sharded over the ranks) and `bands` (cfg4 shape: ONE FD* grid, 16384^2 and 65536^2, in row bands over
+the N GPUs through the sharded planner — NCCL halo exchange, strong scaling, verified by checksum against an unsharded
+plan). `--workload bands|cfg3|cfg5` print one of them as a line of its own; `--no-extras` leaves them out.
 
 Timing: W warm-up steps, then K steps; each step's device time is taken with CUDA events recorded on the
 planner's own stream inside tasi_step (stats.step_ms_device: field fill + seeding + persistent solver), L2 is
@@ -335,6 +338,10 @@ def run_b200(args, rank, world):
                            "verified_how": "every query's start has a finite value (endpoints are free cells)",
                            "per_planner": res}
         torch.cuda.empty_cache()
+        from unige_tasi_path_planners_b200 import sharded_bench
+        sides = tuple(int(v) for v in os.environ.get("TASI_BENCH_BAND_SIDES", "16384,65536").split(",") if v)
+        extras["bands"] = sharded_bench.measure(rank, world, local, steps=max(1, min(args.steps, 3)), warmup=1, sides=sides)
+        torch.cuda.empty_cache()
     if rank == 0:
         ms_per_step = dev_ms_max / args.steps
         value = world * cells / (ms_per_step / 1e3) / 1e6
@@ -382,8 +389,8 @@ def main():
         run_reference(args, rank)
         return
     if args.workload == "bands":
-        from unige_tasi_path_planners_b200 import bands
-        bands.bench_main(args, rank, world)
+        from unige_tasi_path_planners_b200 import sharded_bench
+        sharded_bench.bench_main(args, rank, world)
         return
     if args.workload == "cfg5":
         from unige_tasi_path_planners_b200 import batch

@@ -1,4 +1,9 @@
-"""Row-band sharding of one large grid across GPUs (BASELINE.json cfg4).
+"""Row-band sharding of one large grid, driven from Python over the tasi_band_* primitives.
+
+The PRODUCT path for a sharded grid is the sharded planner inside libtasi_gpu.so (tasi_create_sharded /
+tasi_create_sharded_rank, csrc/tasi_shard.cuh; planner.ShardedPlanner; bench record in sharded_bench.py). This module is
+the protocol it grew out of, kept because it states the exchange protocol in a form that runs on CPU tensors with gloo
+(tests/test_bands.py, world size 2 and 3) and on one GPU over the band primitives of the C ABI.
 
 The reference has no multi-device path; this is the sharded form of the same fixed-point solve.
 Band r owns a contiguous range of element rows plus one halo row of values on each open side. One outer
@@ -379,87 +384,3 @@ def solve_sharded_local(kind, cmap, goal, parts, level=None, device=0, occ=1.0, 
     for b in bands:
         b.close()
     return field, outer, stats
-
-
-# ---- bench.py --workload bands -------------------------------------------------------------------------------
-def bench_main(args, rank, world):
-    """FD* initial plan of ONE side x side synthetic grid cut into `world` row bands, one per GPU (cfg4 shape;
-    the side defaults to 16384 so the default run stays within minutes — pass --side 65536 for the named size).
-    value = side^2 / time to global convergence (max over ranks), scaling "strong"."""
-    import json
-    import os
-    import time
-
-    import torch
-    import torch.distributed as dist
-    from . import synth
-
-    local = int(os.environ.get("LOCAL_RANK", rank))
-    torch.cuda.set_device(local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    side = args.side if args.side != 4096 else 16384
-    kind = _planner.FD
-    start, goal = synth.default_endpoints(side, side)
-    per_rank = int(os.environ.get("TASI_BANDS_PER_GPU", "1"))
-
-    def make(g, parts):
-        b = GpuBand(kind, 1, side, side, parts, g, device=local)
-        b.synth_map(3, 10, start, goal)
-        b.set_endpoints(start, goal)
-        return b
-
-    bs = BandSet(rank, world, per_rank, make)
-    band = bs.bands[bs.ids[0]]
-    comm = DistComm(dist, rank, world, device=torch.device("cuda", local))
-
-    def barrier():
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    k_phases = int(os.environ.get("TASI_BAND_PHASES", "2"))  # 0 = converge fully between exchanges
-
-    def solve():
-        if k_phases > 0:
-            return run_bandset_ordered(bs, comm, k_phases)
-        assert per_rank == 1, "the unordered protocol takes one band per rank"
-        return run_bands(band, comm)
-
-    outer = 0
-    for _ in range(args.warmup):
-        outer = solve()
-    barrier()
-    t0 = time.perf_counter()
-    kernel_ms = 0.0
-    visits = 0
-    for _ in range(args.steps):
-        outer = solve()
-        for b in bs.bands.values():
-            st = b.stats()
-            kernel_ms += st["kernel_ms_solve"]
-            visits += st["tile_visits"]
-    barrier()
-    dt = time.perf_counter() - t0
-    tm = torch.tensor([dt, kernel_ms], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(tm, op=dist.ReduceOp.MAX)
-    if rank == 0:
-        ms = float(tm[0]) / args.steps * 1e3
-        cells = side * side
-        print(json.dumps({
-            "metric": "Mcells/s to convergence (initial plan), FD* %dx%d in row bands" % (side, side),
-            "value": cells / (ms / 1e3) / 1e6, "unit": "Mcells/s", "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong",
-            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "bands (cfg4 shape)", "planner": "FD* level 1", "grid": "%dx%d" % (side, side),
-                       "bands": world * per_rank, "bands_per_gpu": per_rank, "distribution": "cyclic", "halo_exchanges_per_plan": outer, "threshold_widths_per_exchange": k_phases, "collective": "NCCL send/recv of one "
-                       "boundary row per neighbour + all-reduce of lowered-halo counts per outer iteration",
-                       "timing": "wall clock between barriers (host-driven outer loop), max over ranks"},
-            "work": {"solver_kernel_ms_max_rank": float(tm[1]) / args.steps,
-                     "tile_visits_per_tile_rank0": visits / args.steps / max(sum(b.stats()["tiles"] for b in
-                                                                                   bs.bands.values()), 1)}}), flush=True)
-    bs.close()
-    if world > 1:
-        dist.destroy_process_group()

@@ -20,6 +20,7 @@
 using namespace tasi;
 
 struct tasi_shard;
+static thread_local std::string g_create_err = "null planner";
 
 struct tasi_planner {
     tasi_shard *shard = nullptr;  // set on the handle of a sharded planner (tasi_shard.cuh): every entry point forwards
@@ -813,7 +814,7 @@ int tasi_get_stats(tasi_planner *p, tasi_stats *out) {
 }
 
 const char *tasi_last_error(tasi_planner *p) {
-    if (!p) return "null planner";
+    if (!p) return g_create_err.c_str();  // no handle: why the last tasi_create* of this thread failed
     return p->shard ? p->shard->err.c_str() : p->err.c_str();
 }
 
@@ -1135,7 +1136,7 @@ int tasi_create_sharded(int kind, int level, const int *device_ids, int n_dev, t
         for (int j = 0; j < i; ++j) distinct = distinct && device_ids[j] != device_ids[i];
     }
     for (ShardMember &m : s->local)
-        if (shard_init_member(s, m) != TASI_OK) { shard_destroy(s); return TASI_ERR_CUDA; }
+        if (shard_init_member(s, m) != TASI_OK) { g_create_err = s->err; shard_destroy(s); return TASI_ERR_CUDA; }
     // ranks of one process read each other's buffers directly: map every pair of distinct devices
     bool peers = true;
     for (int i = 0; i < n_dev && peers; ++i)
@@ -1151,11 +1152,20 @@ int tasi_create_sharded(int kind, int level, const int *device_ids, int n_dev, t
         }
     const char *want = getenv("TASI_SHARD_NCCL");
     s->use_nccl = n_dev > 1 && distinct && ((want && atoi(want) != 0) || !peers);
-    if (n_dev > 1 && !peers && !distinct) { shard_destroy(s); return TASI_ERR_CUDA; }
+    if (n_dev > 1 && !peers && !distinct) {
+        g_create_err = "create_sharded: repeated devices without peer access";
+        shard_destroy(s);
+        return TASI_ERR_CUDA;
+    }
     if (s->use_nccl) {
         NcclApi &N = nccl_api();
         std::vector<ncclComm_t> comms(n_dev);
-        if (!N.load() || N.CommInitAll(comms.data(), n_dev, device_ids) != ncclSuccess) { shard_destroy(s); return TASI_ERR_CUDA; }
+        ncclResult_t r = ncclSuccess;
+        if (!N.load() || (r = N.CommInitAll(comms.data(), n_dev, device_ids)) != ncclSuccess) {
+            g_create_err = N.handle ? std::string("ncclCommInitAll: ") + N.GetErrorString(r) : N.err;
+            shard_destroy(s);
+            return TASI_ERR_CUDA;
+        }
         for (int i = 0; i < n_dev; ++i) s->local[i].comm = comms[i];
     }
     return shard_finish_create(s, kind, level, out);
@@ -1164,9 +1174,9 @@ int tasi_create_sharded(int kind, int level, const int *device_ids, int n_dev, t
 int tasi_nccl_unique_id(void *out128) {
     if (!out128) return TASI_ERR_ARG;
     NcclApi &N = nccl_api();
-    if (!N.load()) return TASI_ERR_CUDA;
+    if (!N.load()) { g_create_err = N.err; return TASI_ERR_CUDA; }
     ncclUniqueId id;
-    if (N.GetUniqueId(&id) != ncclSuccess) return TASI_ERR_CUDA;
+    if (N.GetUniqueId(&id) != ncclSuccess) { g_create_err = "ncclGetUniqueId failed"; return TASI_ERR_CUDA; }
     memcpy(out128, &id, sizeof id);
     return TASI_OK;
 }
@@ -1186,14 +1196,16 @@ int tasi_create_sharded_rank(int kind, int level, int device, int rank, int n_ra
     s->local.resize(1);
     s->local[0].rank = rank;
     s->local[0].device = device;
-    if (shard_init_member(s, s->local[0]) != TASI_OK) { shard_destroy(s); return TASI_ERR_CUDA; }
+    if (shard_init_member(s, s->local[0]) != TASI_OK) { g_create_err = s->err; shard_destroy(s); return TASI_ERR_CUDA; }
     s->use_nccl = n_ranks > 1;
     if (s->use_nccl) {
         NcclApi &N = nccl_api();
         ncclUniqueId id;
         memcpy(&id, nccl_unique_id, sizeof id);
         cudaSetDevice(device);
-        if (!N.load() || N.CommInitRank(&s->local[0].comm, n_ranks, id, rank) != ncclSuccess) {
+        ncclResult_t r = ncclSuccess;
+        if (!N.load() || (r = N.CommInitRank(&s->local[0].comm, n_ranks, id, rank)) != ncclSuccess) {
+            g_create_err = N.handle ? std::string("ncclCommInitRank: ") + N.GetErrorString(r) : N.err;
             shard_destroy(s);
             return TASI_ERR_CUDA;
         }

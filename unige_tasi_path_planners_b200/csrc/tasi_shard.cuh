@@ -819,12 +819,13 @@ int shard_collect_stats(tasi_shard *s, bool fresh) {
         SH_TRY(s, cudaEventElapsedTime(&dev_ms, m.ev_t0, m.ev_t1));
         s->stats.step_ms_device = std::max(s->stats.step_ms_device, dev_ms);
     }
-    double v[1] = {busy_max}, out = 0;
-    int rc = shard_allreduce_host(s, v, true, &out);
+    std::vector<double> v(s->local.size(), busy_max);
+    double out = 0;
+    int rc = shard_allreduce_host(s, v.data(), true, &out);
     if (rc != TASI_OK) return rc;
     s->sstats.solver_ms_max_rank = (float) out;
-    v[0] = -busy_min;
-    rc = shard_allreduce_host(s, v, true, &out);
+    v.assign(s->local.size(), -busy_min);
+    rc = shard_allreduce_host(s, v.data(), true, &out);
     if (rc != TASI_OK) return rc;
     s->sstats.solver_ms_min_rank = (float) -out;
     s->stats.kernel_ms_solve = s->sstats.solver_ms_max_rank;

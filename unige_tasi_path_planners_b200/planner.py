@@ -368,7 +368,8 @@ class ShardedPlanner(GpuPlanner):
             rc = self._L.tasi_create_sharded_rank(kind, level, device, rank, n_ranks, buf, C.byref(h))
             self.device = device
         if rc != _lib.OK:
-            raise TasiError(rc, "tasi_create_sharded failed (no CUDA device / NCCL? there is no CPU fallback)")
+            raise TasiError(rc, "tasi_create_sharded failed: %s (there is no CPU fallback)"
+                            % self._L.tasi_last_error(None).decode())
         self._h = h
         self.level = level
         self.u_time = self.p_time = 0.0

@@ -168,19 +168,33 @@ int tasi_create_sharded(int kind, int level, const int *device_ids, int n_dev, t
 int tasi_nccl_unique_id(void *out128);
 int tasi_create_sharded_rank(int kind, int level, int device, int rank, int n_ranks, const void *nccl_unique_id,
                              tasi_planner **out);
-/* Bands per device (default 4, TASI_BANDS_PER_GPU) and threshold widths of the tile schedule between two exchanges
- * (default 2, TASI_BAND_PHASES); values < 1 keep the current setting. Before set_map. */
+/* Bands per device (default 4, TASI_BANDS_PER_GPU) and threshold widths of the tile schedule between two exchanges of
+ * the iteration-based mode (default 1, TASI_BAND_PHASES); values < 1 keep the current setting. Before set_map. */
 int tasi_shard_config(tasi_planner *p, int bands_per_device, int phases_per_exchange);
+/* Fused mode on (default) / off (TASI_SHARD_FUSED=0): off keeps the iteration-based exchange (NCCL or peer reads). */
+int tasi_shard_set_fused(tasi_planner *p, int enabled);
+/* Fused mode across processes: after every set_map / synth_map each rank exports tasi_shard_ipc_size() bytes (CUDA IPC
+ * handles of its value field, tile states, keys, work queue and control blocks), the caller all-gathers them (by rank)
+ * and hands the whole array to every rank. Without it a multi-process sharded planner runs the NCCL iterations. */
+int tasi_shard_ipc_size(void);
+int tasi_shard_ipc_export(tasi_planner *p, void *blob);
+int tasi_shard_ipc_import(tasi_planner *p, const void *blobs_by_rank);
 
 typedef struct tasi_shard_stats {
     int32_t n_ranks, bands, bands_per_rank, rows_per_band;
-    int32_t nccl;               /* 1: NCCL send/recv + all-reduce, 0: peer-mapped reads (ranks of one process) */
-    int32_t pad;
-    uint64_t exchanges;         /* outer iterations of the relax loop (incl. the few empty ones queued past convergence) */
-    uint64_t inval_exchanges;   /* outer iterations of the invalidate loop of a replan */
+    int32_t nccl;               /* 1: NCCL send/recv + all-reduce per outer iteration; 0: peer-mapped memory */
+    int32_t fused;              /* 1: fused mode — one persistent launch per GPU, boundary rows and tile activations go
+                                 * straight into the neighbour's memory during the tile visits, thresholds advance globally */
+    uint64_t exchanges;         /* outer iterations of the relax loop (0 in fused mode) */
+    uint64_t inval_exchanges;   /* outer iterations of the invalidate loop of a replan (0 in fused mode) */
+    uint64_t fused_launches;    /* fused launches of the step (1 per phase of a plan / replan) */
+    uint64_t remote_activations; /* tile activations sent to other ranks (fused mode), summed over the ranks */
     float wall_ms;              /* host wall clock of the step */
-    float solver_ms_max_rank;   /* time inside the persistent solver launches, busiest and idlest rank: */
-    float solver_ms_min_rank;   /* solver_ms_max_rank / wall_ms is the share of the step spent solving */
+    float solver_ms_max_rank;   /* time inside the persistent solver launches, busiest and idlest rank */
+    float solver_ms_min_rank;
+    float busy_frac_max_rank;   /* share of the CTA time spent on tiles (staging, relaxing, writing back) rather than */
+    float busy_frac_min_rank;   /* waiting for one, busiest and idlest rank */
+    float pad;
 } tasi_shard_stats;
 int tasi_shard_get_stats(tasi_planner *p, tasi_shard_stats *out);
 

@@ -42,6 +42,6 @@ for per, k in settings:
     ok = p.field_checksum() == want
     ss, st = best[1], best[2]
     print(json.dumps({"n_dev": ndev, "bands_per_gpu": ss["bands_per_rank"], "phases": k, "ms": best[0], "exchanges": ss["exchanges"],
-                      "solver_ms_max": ss["solver_ms_max_rank"], "solver_ms_min": ss["solver_ms_min_rank"], "nccl": ss["nccl"],
+                      "solver_ms_max": ss["solver_ms_max_rank"], "solver_ms_min": ss["solver_ms_min_rank"], "nccl": ss["nccl"], "fused": ss["fused"], "remote_act": ss["remote_activations"], "busy": [ss["busy_frac_min_rank"], ss["busy_frac_max_rank"]],
                       "visits_per_tile": st["tile_visits"] / st["tiles"], "verified": ok}), flush=True)
     p.close()

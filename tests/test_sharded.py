@@ -60,7 +60,13 @@ def test_sharded_plan_equals_single_device(kind, ranks, per_rank):
     got = p.read_field()
     same(kind, got, want)
     ss = p.shard_stats()
-    assert ss["n_ranks"] == ranks and ss["bands"] <= ranks * per_rank and ss["exchanges"] >= 1
+    assert ss["n_ranks"] == ranks and ss["bands"] <= ranks * per_rank
+    # one rank: the fused mode (border rows and activations written straight across the band edges, global phases);
+    # several ranks on ONE device: the exchange iterations (persistent kernels of two ranks must not share a GPU)
+    assert ss["fused"] == (1 if ranks == 1 else 0)
+    assert (ss["fused_launches"] >= 1) if ss["fused"] else (ss["exchanges"] >= 1)
+    if ss["fused"] and ss["bands"] > 1:
+        assert ss["remote_activations"] > 0
     if kind != 1:
         assert p.field_checksum() == ref.field_checksum()
     assert np.array_equal(p.read_map(), cmap)
@@ -74,13 +80,14 @@ def test_sharded_plan_equals_single_device(kind, ranks, per_rank):
 
 @pytest.mark.parametrize("kind", KINDS)
 @pytest.mark.parametrize("mode", ["mixed", "raise", "lower"])
-def test_sharded_replan_equals_from_scratch(kind, mode):
+@pytest.mark.parametrize("ranks,per_rank", [(2, 2), (1, 4)])
+def test_sharded_replan_equals_from_scratch(kind, mode, ranks, per_rank):
     """patch_map + step on the sharded grid (invalidate across bands, then re-propagate) == a single-device plan of the
     patched map; the patch straddles band boundaries."""
     L, W = 420, 260
     start, goal = (5.0, 5.0), (float(L - 6), float(W - 6))
     cmap = synth.synth_map(61, L, W, 10, start, goal)
-    p = sharded(kind, 2, 2)
+    p = sharded(kind, ranks, per_rank)
     p.set_map(cmap)
     p.set_start(*start)
     p.set_goal(*goal)
@@ -104,7 +111,8 @@ def test_sharded_replan_equals_from_scratch(kind, mode):
     same(kind, p.read_field(), ref.read_field())
     assert np.array_equal(p.read_map(), patched)
     if mode != "lower":
-        assert p.shard_stats()["inval_exchanges"] >= 1
+        ss = p.shard_stats()
+        assert ss["inval_exchanges"] >= 1 or ss["fused_launches"] >= 2
     # a second patch right away, and a step without a new start in between changes nothing (ReplannerBase.h:56-59)
     patch2 = np.full((30, 40), 3, np.uint8)
     p.patch_map(patch2, 120, 100)
@@ -134,6 +142,26 @@ def test_sharded_walk_equals_single_device_walk(kind):
     assert np.array_equal(got[0]["path"], want[0]["path"])
     assert got[0]["total_cost"] == want[0]["total_cost"] and got[0]["status"] == want[0]["status"]
     p.close(); ref.close()
+
+
+@pytest.mark.parametrize("kind", KINDS)
+def test_fused_and_iteration_modes_agree(kind):
+    L, W = 500, 333
+    start, goal = (250.0, 160.0), (10.0, 300.0)   # a goal in the first band: fronts run up AND down the stack
+    cmap = synth.synth_map(81, L, W, 12, start, goal)
+    ref = single(kind, cmap, start, goal)
+    want = ref.read_field()
+    for fused in (True, False):
+        p = sharded(kind, 1, 5)
+        p.set_fused(fused)
+        p.set_map(cmap)
+        p.set_start(*start)
+        p.set_goal(*goal)
+        assert p.step() == 0
+        assert p.shard_stats()["fused"] == int(fused)
+        same(kind, p.read_field(), want)
+        p.close()
+    ref.close()
 
 
 def test_sharded_flags_and_errors():

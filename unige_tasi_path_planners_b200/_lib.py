@@ -44,8 +44,10 @@ class Stats(C.Structure):
 
 class ShardStats(C.Structure):
     _fields_ = [("n_ranks", C.c_int32), ("bands", C.c_int32), ("bands_per_rank", C.c_int32), ("rows_per_band", C.c_int32),
-                ("nccl", C.c_int32), ("pad", C.c_int32), ("exchanges", C.c_uint64), ("inval_exchanges", C.c_uint64),
-                ("wall_ms", C.c_float), ("solver_ms_max_rank", C.c_float), ("solver_ms_min_rank", C.c_float)]
+                ("nccl", C.c_int32), ("fused", C.c_int32), ("exchanges", C.c_uint64), ("inval_exchanges", C.c_uint64),
+                ("fused_launches", C.c_uint64), ("remote_activations", C.c_uint64),
+                ("wall_ms", C.c_float), ("solver_ms_max_rank", C.c_float), ("solver_ms_min_rank", C.c_float),
+                ("busy_frac_max_rank", C.c_float), ("busy_frac_min_rank", C.c_float), ("pad", C.c_float)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_ if n != "pad"}
@@ -90,6 +92,10 @@ SIGNATURES = {
     "tasi_nccl_unique_id": (C.c_int, [C.c_void_p]),
     "tasi_create_sharded_rank": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.POINTER(C.c_void_p)]),
     "tasi_shard_config": (C.c_int, [C.c_void_p, C.c_int, C.c_int]),
+    "tasi_shard_set_fused": (C.c_int, [C.c_void_p, C.c_int]),
+    "tasi_shard_ipc_size": (C.c_int, []),
+    "tasi_shard_ipc_export": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "tasi_shard_ipc_import": (C.c_int, [C.c_void_p, C.c_void_p]),
     "tasi_shard_get_stats": (C.c_int, [C.c_void_p, C.POINTER(ShardStats)]),
     "tasi_field_checksum": (C.c_int, [C.c_void_p, _u64p]),
     "tasi_extract_paths": (C.c_int, [C.c_void_p, _f32p, _f32p, _i32p, C.c_int, C.c_int, C.c_int, C.c_int, _f32p, C.c_int,

@@ -25,6 +25,9 @@ static thread_local std::string g_create_err = "null planner";
 struct tasi_planner {
     tasi_shard *shard = nullptr;  // set on the handle of a sharded planner (tasi_shard.cuh): every entry point forwards
     int band_rt = 0;              // > 0: this grid is a stack of row bands of band_rt tile rows (a member of a shard)
+    const FusedTopo *ft = nullptr;  // fused multi-GPU mode (device pointer; tasi_shard.cuh), nullptr = off
+    int *inbox = nullptr;
+    int inbox_cap = 0;
     int kind = TASI_FD, level = 0, device = 0;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, evs0 = nullptr, evs1 = nullptr;
@@ -145,6 +148,10 @@ GridDesc make_desc(const tasi_planner *p) {
     d.n_focus = 0;
     d.focus_slack = p->focus_slack;
     d.band_rt = p->band_rt;
+    d.ft = p->ft;
+    d.inbox = p->inbox;
+    d.inbox_cap = p->inbox_cap;
+    d.fmode = 0;
     if (p->focus && !p->open_top && !p->open_bottom && p->band_rt == 0) {
         // Graph::set_start: start_cell_ = Cell(start) rounds (Cell.cpp:20-21); FD*/MFD* wait for the cell's four
         // corner nodes (FieldDPlanner_impl.h:12, Cell.cpp:58-60), MS-DFM for the cell itself
@@ -1107,6 +1114,7 @@ int shard_finish_create(tasi_shard *s, int kind, int level, tasi_planner **out) 
         const int v = atoi(e);
         if (v >= 1 && v <= 64) s->k_phases = v;
     }
+    if (const char *e = getenv("TASI_SHARD_FUSED")) s->want_fused = atoi(e) != 0;
     *out = top;
     return TASI_OK;
 }
@@ -1218,6 +1226,111 @@ int tasi_shard_config(tasi_planner *p, int bands_per_device, int phases_per_exch
     if (!p->shard->initialize_graph) return sh_fail(p->shard, TASI_ERR_STATE, "shard_config must precede set_map");
     if (bands_per_device >= 1) p->shard->want_per_rank = std::min(bands_per_device, 64);
     if (phases_per_exchange >= 1) p->shard->k_phases = std::min(phases_per_exchange, 64);
+    return TASI_OK;
+}
+
+int tasi_shard_set_fused(tasi_planner *p, int enabled) {
+    if (!p || !p->shard) return TASI_ERR_ARG;
+    tasi_shard *s = p->shard;
+    s->want_fused = enabled != 0;
+    if (!s->want_fused) {
+        s->fused = false;
+        for (ShardMember &m : s->local) m.p->ft = nullptr;
+        return TASI_OK;
+    }
+    return s->initialize_graph || sh_multi_process(s) ? TASI_OK : shard_connect_local(s);
+}
+
+namespace {
+struct ShardIpcBlob {
+    cudaIpcMemHandle_t g, state, key, queue, ctl, fc, inbox;
+    int64_t gpitch;
+    int qmask, far_cap, TY, inbox_cap, rank, valid;
+};
+}  // namespace
+
+int tasi_shard_ipc_size(void) { return (int) ((sizeof(ShardIpcBlob) + 63) / 64 * 64); }
+
+int tasi_shard_ipc_export(tasi_planner *p, void *blob) {
+    if (!p || !p->shard || !blob) return TASI_ERR_ARG;
+    tasi_shard *s = p->shard;
+    if (s->initialize_graph || s->local.size() != 1) return sh_fail(s, TASI_ERR_STATE, "ipc_export: needs a map, one rank per process");
+    ShardMember &m = s->local[0];
+    tasi_planner *q = m.p;
+    ShardIpcBlob b;
+    memset(&b, 0, sizeof b);
+    SH_TRY(s, cudaSetDevice(m.device));
+    SH_TRY(s, cudaIpcGetMemHandle(&b.g, q->g_base));
+    SH_TRY(s, cudaIpcGetMemHandle(&b.state, q->state));
+    SH_TRY(s, cudaIpcGetMemHandle(&b.key, q->key));
+    SH_TRY(s, cudaIpcGetMemHandle(&b.queue, q->queue));
+    SH_TRY(s, cudaIpcGetMemHandle(&b.ctl, q->ctl));
+    SH_TRY(s, cudaIpcGetMemHandle(&b.fc, m.fc));
+    SH_TRY(s, cudaIpcGetMemHandle(&b.inbox, q->inbox));
+    b.gpitch = q->gpitch; b.qmask = (int) (q->qsize - 1); b.far_cap = q->far_cap; b.TY = q->TY;
+    b.inbox_cap = q->inbox_cap; b.rank = m.rank; b.valid = 1;
+    memset(blob, 0, tasi_shard_ipc_size());
+    memcpy(blob, &b, sizeof b);
+    return TASI_OK;
+}
+
+int tasi_shard_ipc_import(tasi_planner *p, const void *blobs_by_rank) {
+    if (!p || !p->shard || !blobs_by_rank) return TASI_ERR_ARG;
+    tasi_shard *s = p->shard;
+    if (s->initialize_graph || s->local.size() != 1) return sh_fail(s, TASI_ERR_STATE, "ipc_import: needs a map, one rank per process");
+    s->fused = false;
+    ShardMember &m = s->local[0];
+    m.p->ft = nullptr;
+    if (!s->want_fused || s->world == 1) return s->world == 1 ? shard_connect_local(s) : TASI_OK;
+    SH_TRY(s, cudaSetDevice(m.device));
+    shard_close_ipc(m);
+    const size_t stride = tasi_shard_ipc_size();
+    auto blob_of = [&](int r) {
+        ShardIpcBlob b;
+        memcpy(&b, (const char *) blobs_by_rank + (size_t) r * stride, sizeof b);
+        return b;
+    };
+    auto open = [&](const cudaIpcMemHandle_t &h, void **out) -> int {
+        SH_TRY(s, cudaIpcOpenMemHandle(out, h, cudaIpcMemLazyEnablePeerAccess));
+        m.ipc_open.push_back(*out);
+        return TASI_OK;
+    };
+    FusedCtl *fcs[FUSED_MAX_RANKS] = {};
+    for (int r = 0; r < s->world; ++r) {
+        if (r == m.rank) { fcs[r] = m.fc; continue; }
+        const ShardIpcBlob b = blob_of(r);
+        if (!b.valid || b.rank != r) return sh_fail(s, TASI_ERR_ARG, "ipc_import: blob " + std::to_string(r) + " is not rank " + std::to_string(r) + "'s");
+        void *q = nullptr;
+        int rc = open(b.fc, &q);
+        if (rc != TASI_OK) return rc;
+        fcs[r] = (FusedCtl *) q;
+    }
+    GridDesc nb[2];
+    const int prev = (m.rank + s->world - 1) % s->world, next = (m.rank + 1) % s->world;
+    for (int k = 0; k < 2; ++k) {
+        const int r = k == 0 ? prev : next;
+        if (k == 1 && next == prev) { nb[1] = nb[0]; break; }
+        const ShardIpcBlob b = blob_of(r);
+        GridDesc d = make_desc(m.p);  // same geometry conventions on every rank; the pointers are replaced below
+        void *g = nullptr, *st = nullptr, *ky = nullptr, *qu = nullptr, *ct = nullptr, *ib = nullptr;
+        int rc;
+        if ((rc = open(b.g, &g)) != TASI_OK || (rc = open(b.state, &st)) != TASI_OK || (rc = open(b.key, &ky)) != TASI_OK ||
+            (rc = open(b.queue, &qu)) != TASI_OK || (rc = open(b.ctl, &ct)) != TASI_OK || (rc = open(b.inbox, &ib)) != TASI_OK)
+            return rc;
+        d.g = (float *) g + b.gpitch + GMARGIN;
+        d.gpitch = b.gpitch;
+        d.cost = nullptr;
+        d.state = (int *) st; d.key = (int *) ky; d.queue = (int *) qu; d.qmask = (unsigned) b.qmask;
+        d.far = nullptr; d.far_cap = b.far_cap;
+        d.ctl = (DevCtl *) ct;
+        d.inbox = (int *) ib; d.inbox_cap = b.inbox_cap;
+        d.TY = b.TY;
+        d.seed = nullptr; d.xgoals = nullptr;
+        nb[k] = d;
+    }
+    int rc = shard_upload_topo(s, m, nb[0], nb[1], fcs);
+    if (rc != TASI_OK) return rc;
+    s->fused = true;
     return TASI_OK;
 }
 

@@ -192,6 +192,25 @@ __global__ void shard_limit_kernel(ShardCtl *sc, RedPtrs r, int *flag_out) {
     if (flag_out) *flag_out = sc->converged;
 }
 
+// fused mode: queue state and control words before a launch (everything is parked first: enqueue_seeds ordered)
+__global__ void fused_rearm_kernel(GridDesc d, FusedCtl *fc, FusedTopo *topo, int mode, int rank) {
+    DevCtl *c = d.ctl;
+    c->head = c->tail = 0;
+    c->pending = 0;
+    c->done = 0;
+    c->kick = 0;
+    c->focus_hit = 0;
+    c->far_min_bits = INF_BITS;
+    c->limit_bits = INF_BITS;
+    c->thr_bits = mode == 1 ? INF_BITS : 0;
+    c->far_sel = 0;
+    c->far_count[0] = c->far_count[1] = 0;
+    fc->inbox_count = 0;
+    fc->rx = fc->tx = 0;
+    if (rank == 0) fc->active = 0;
+    topo->mode = mode;
+}
+
 __device__ __forceinline__ uint64_t shard_mix64(uint64_t z) {
     z += 0x9E3779B97F4A7C15ULL;
     z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
@@ -236,6 +255,10 @@ struct ShardMember {
     unsigned long long *sum_dev = nullptr;
     cudaEvent_t ev_packed = nullptr, ev_red = nullptr, ev_flag[SHARD_FLAG_RING] = {}, ev_t0 = nullptr, ev_t1 = nullptr;
     ncclComm_t comm = nullptr;
+    // fused mode
+    FusedCtl *fc = nullptr;
+    FusedTopo *topo = nullptr;     // device copy
+    std::vector<void *> ipc_open;  // pointers opened with cudaIpcOpenMemHandle (multi-process form)
     float *buf(int parity, int what, int B, int EY) const { return xbuf + ((size_t) (parity * 4 + what) * B) * EY; }
 };
 
@@ -247,7 +270,9 @@ struct tasi_shard {
     int my_rank = -1;     // >= 0: one rank per process (multi-process form)
     bool use_nccl = false;
     int want_per_rank = 4, per_rank = 1, parts = 1;
-    int k_phases = 2;
+    int k_phases = 1;
+    bool want_fused = true;   // use the fused mode whenever the ranks can map each other's memory
+    bool fused = false;       // ... and they do (set by shard_connect_local / tasi_shard_ipc_import)
     std::vector<ShardMember> local;
     std::vector<ShardBand> bands;
     // geometry
@@ -302,11 +327,25 @@ inline int sh_sub(tasi_shard *s, ShardMember &m, int rc) {
 inline bool sh_node(const tasi_shard *s) { return s->kind != TASI_DFM; }
 inline bool sh_multi_process(const tasi_shard *s) { return s->my_rank >= 0; }
 
+void shard_close_ipc(ShardMember &m) {
+    cudaSetDevice(m.device);
+    for (void *q : m.ipc_open) cudaIpcCloseMemHandle(q);
+    m.ipc_open.clear();
+}
+
 void shard_free_member_buffers(ShardMember &m) {
     cudaSetDevice(m.device);
+    shard_close_ipc(m);
     cudaFree(m.xbuf); cudaFree(m.pack_jobs); cudaFree(m.import_jobs);
     m.xbuf = nullptr; m.pack_jobs = nullptr; m.import_jobs = nullptr;
+    if (m.p) {
+        cudaFree(m.p->inbox);
+        m.p->inbox = nullptr; m.p->inbox_cap = 0; m.p->ft = nullptr;
+    }
 }
+
+int shard_connect_local(tasi_shard *s);
+int shard_sync_all(tasi_shard *s);
 
 // Cut the element rows into bands and (re)allocate every local stack.
 int shard_layout(tasi_shard *s, int W, int L) {
@@ -352,7 +391,11 @@ int shard_layout(tasi_shard *s, int W, int L) {
         SH_TRY(s, cudaMalloc(&m.xbuf, sizeof(float) * 8 * (size_t) B * EY));
         SH_TRY(s, cudaMalloc(&m.pack_jobs, sizeof(PackJob) * 4 * B));
         SH_TRY(s, cudaMalloc(&m.import_jobs, sizeof(ImportJob) * 4 * B));
+        p->inbox_cap = 4 * B * p->TY + 64;  // every border tile of the stack, twice over
+        SH_TRY(s, cudaMalloc(&p->inbox, sizeof(int) * p->inbox_cap));
     }
+    s->fused = false;
+    for (ShardMember &m : s->local) m.p->ft = nullptr;
     // job tables (they hold peer pointers, so they are built once every member's buffers exist)
     for (ShardMember &m : s->local) {
         const int B = per_rank;
@@ -388,6 +431,64 @@ int shard_layout(tasi_shard *s, int W, int L) {
         SH_TRY(s, cudaMemcpy(m.pack_jobs, pj.data(), sizeof(PackJob) * pj.size(), cudaMemcpyHostToDevice));
         SH_TRY(s, cudaMemcpy(m.import_jobs, ij.data(), sizeof(ImportJob) * ij.size(), cudaMemcpyHostToDevice));
     }
+    return shard_connect_local(s);
+}
+
+// Fused mode for the ranks of ONE process: every rank gets the GridDesc of its ring neighbours and the control blocks of
+// all ranks (plain device pointers; distinct devices are peer-mapped at creation). Not with several ranks on one
+// device: their persistent kernels would wait on each other inside one GPU.
+int shard_upload_topo(tasi_shard *s, ShardMember &m, const GridDesc &up, const GridDesc &dn, FusedCtl *const *fcs) {
+    FusedTopo t;
+    memset(&t, 0, sizeof t);
+    t.world = s->world; t.rank = m.rank; t.parts = s->parts; t.mode = 0;
+    t.nbr[0] = up; t.nbr[1] = dn;
+    t.nbr[0].ft = nullptr; t.nbr[1].ft = nullptr;
+    for (int r = 0; r < s->world; ++r) t.fc[r] = fcs[r];
+    SH_TRY(s, cudaSetDevice(m.device));
+    SH_TRY(s, cudaMemcpy(m.topo, &t, sizeof t, cudaMemcpyHostToDevice));
+    m.p->ft = m.topo;
+    return TASI_OK;
+}
+
+int shard_connect_local(tasi_shard *s) {
+    s->fused = false;
+    if (!s->want_fused || sh_multi_process(s) || s->use_nccl) return TASI_OK;
+    for (size_t i = 0; i < s->local.size(); ++i)
+        for (size_t j = 0; j < i; ++j)
+            if (s->local[i].device == s->local[j].device) return TASI_OK;
+    FusedCtl *fcs[FUSED_MAX_RANKS] = {};
+    for (ShardMember &m : s->local) fcs[m.rank] = m.fc;
+    for (ShardMember &m : s->local) {
+        const ShardMember &up = s->local[(m.rank + s->world - 1) % s->world], &dn = s->local[(m.rank + 1) % s->world];
+        int rc = shard_upload_topo(s, m, make_desc(up.p), make_desc(dn.p), fcs);
+        if (rc != TASI_OK) return rc;
+    }
+    s->fused = true;
+    return TASI_OK;
+}
+
+// One fused launch per rank: everything flagged is parked, the solvers of all ranks run until the coordinator ends them.
+int shard_fused_run(tasi_shard *s, int mode) {
+    for (ShardMember &m : s->local) {
+        tasi_planner *p = m.p;
+        SH_TRY(s, cudaSetDevice(m.device));
+        int rc = ensure_cost_stats(p);
+        if (rc != TASI_OK) return sh_sub(s, m, rc);
+        GridDesc d = make_desc(p);
+        d.n_focus = 0;
+        d.fmode = mode;
+        const int nt = p->TX * p->TY;
+        fused_rearm_kernel<<<1, 1, 0, p->stream>>>(d, m.fc, m.topo, mode, m.rank);
+        if (mode == 0) seed_keys_kernel<<<std::min((nt + 7) / 8, p->num_sms * 8), 256, 0, p->stream>>>(d);
+        enqueue_seeds_kernel<<<std::min((nt + 255) / 256, 1024), 256, 0, p->stream>>>(d, 1);
+        const int cap = s->max_blocks > 0 ? s->max_blocks : p->max_blocks;
+        const int nblocks = (cap > 0 && cap < p->solver_blocks) ? cap : p->solver_blocks;
+        pick_solver(p->kind, mode, p->strip)<<<nblocks, TS * TS / p->strip, 0, p->stream>>>(d);
+        SH_TRY(s, cudaGetLastError());
+    }
+    int rc = shard_sync_all(s);
+    if (rc != TASI_OK) return rc;
+    s->sstats.fused_launches += 1;
     return TASI_OK;
 }
 
@@ -667,6 +768,7 @@ int shard_reset_ctl(tasi_shard *s, bool counters, float limit, float step) {
 
 // The relax loop (initial plan, or phase 2 of a replan): see the header of this file.
 int shard_relax_loop(tasi_shard *s) {
+    if (s->fused) return shard_fused_run(s, 0);
     // common step of the limit: k_phases threshold widths of the widest band
     std::vector<double> deltas;
     for (ShardMember &m : s->local) {
@@ -760,6 +862,7 @@ int shard_relax_loop(tasi_shard *s) {
 // Phase 1 of a replan on the sharded grid: invalidate in every band, swap boundary rows, replace the halos, until no
 // halo changes anywhere. Host-paced (a replan's invalidated region is small and the loop runs a handful of times).
 int shard_invalidate_loop(tasi_shard *s) {
+    if (s->fused) return shard_fused_run(s, 1);
     int rc = shard_reset_ctl(s, false, INFINITY, 0.0f);
     if (rc != TASI_OK) return rc;
     for (int it = 0; it < (1 << 20); ++it) {
@@ -792,7 +895,7 @@ int shard_invalidate_loop(tasi_shard *s) {
 }
 
 int shard_collect_stats(tasi_shard *s, bool fresh) {
-    double busy_max = 0, busy_min = INFINITY;
+    double busy_max = 0, busy_min = INFINITY, bf_max = 0, bf_min = INFINITY, rtx = 0;
     for (ShardMember &m : s->local) {
         SH_TRY(s, cudaSetDevice(m.device));
         DevCtl h;
@@ -815,6 +918,13 @@ int shard_collect_stats(tasi_shard *s, bool fresh) {
         const double ms = (double) h.busy_ns / 1e6;
         busy_max = std::max(busy_max, ms);
         busy_min = std::min(busy_min, ms);
+        const double work = (double) h.cyc_stage + (double) h.cyc_relax + (double) h.cyc_post, all = work + (double) h.cyc_pop;
+        const double bf = all > 0 ? work / all : 0.0;
+        bf_max = std::max(bf_max, bf);
+        bf_min = std::min(bf_min, bf);
+        FusedCtl fh;
+        SH_TRY(s, cudaMemcpy(&fh, m.fc, sizeof fh, cudaMemcpyDeviceToHost));
+        rtx += (double) fh.tx;
         float dev_ms = 0;
         SH_TRY(s, cudaEventElapsedTime(&dev_ms, m.ev_t0, m.ev_t1));
         s->stats.step_ms_device = std::max(s->stats.step_ms_device, dev_ms);
@@ -829,6 +939,19 @@ int shard_collect_stats(tasi_shard *s, bool fresh) {
     if (rc != TASI_OK) return rc;
     s->sstats.solver_ms_min_rank = (float) -out;
     s->stats.kernel_ms_solve = s->sstats.solver_ms_max_rank;
+    v.assign(s->local.size(), bf_max);
+    rc = shard_allreduce_host(s, v.data(), true, &out);
+    if (rc != TASI_OK) return rc;
+    s->sstats.busy_frac_max_rank = (float) out;
+    v.assign(s->local.size(), -bf_min);
+    rc = shard_allreduce_host(s, v.data(), true, &out);
+    if (rc != TASI_OK) return rc;
+    s->sstats.busy_frac_min_rank = (float) -out;
+    v.assign(s->local.size(), 0.0);
+    v[0] = rtx;
+    rc = shard_allreduce_host(s, v.data(), false, &out);
+    if (rc != TASI_OK) return rc;
+    s->sstats.remote_activations = (uint64_t) out;
     (void) fresh;
     return TASI_OK;
 }
@@ -849,7 +972,8 @@ int shard_step(tasi_shard *s, float *u_ms, float *p_ms, uint64_t *n_updated, uin
     s->sstats.bands = s->parts;
     s->sstats.bands_per_rank = s->per_rank;
     s->sstats.rows_per_band = s->R;
-    s->sstats.nccl = (s->use_nccl && s->world > 1) ? 1 : 0;
+    s->sstats.nccl = (s->use_nccl && s->world > 1 && !s->fused) ? 1 : 0;
+    s->sstats.fused = s->fused ? 1 : 0;
     int rc;
     const double t0 = now_ms();
     for (ShardMember &m : s->local) {
@@ -1015,7 +1139,7 @@ void shard_destroy(tasi_shard *s) {
         if (m.p && m.p->stream) cudaStreamSynchronize(m.p->stream);
         if (m.comm && nccl_api().CommDestroy) nccl_api().CommDestroy(m.comm);
         shard_free_member_buffers(m);
-        cudaFree(m.sctl); cudaFree(m.sum_dev);
+        cudaFree(m.sctl); cudaFree(m.sum_dev); cudaFree(m.fc); cudaFree(m.topo);
         cudaFreeHost(m.flags_host);
         if (m.ev_packed) cudaEventDestroy(m.ev_packed);
         if (m.ev_red) cudaEventDestroy(m.ev_red);
@@ -1035,6 +1159,9 @@ int shard_init_member(tasi_shard *s, ShardMember &m) {
     SH_TRY(s, cudaMalloc(&m.sctl, sizeof(ShardCtl)));
     SH_TRY(s, cudaMemset(m.sctl, 0, sizeof(ShardCtl)));
     SH_TRY(s, cudaMalloc(&m.sum_dev, 16));
+    SH_TRY(s, cudaMalloc(&m.fc, sizeof(FusedCtl)));
+    SH_TRY(s, cudaMemset(m.fc, 0, sizeof(FusedCtl)));
+    SH_TRY(s, cudaMalloc(&m.topo, sizeof(FusedTopo)));
     SH_TRY(s, cudaHostAlloc(&m.flags_host, sizeof(int) * SHARD_FLAG_RING, cudaHostAllocMapped));
     memset(m.flags_host, 0, sizeof(int) * SHARD_FLAG_RING);
     SH_TRY(s, cudaEventCreateWithFlags(&m.ev_packed, cudaEventDisableTiming));

@@ -96,6 +96,11 @@ struct GridDesc {
     // a stack of row bands in one grid (sharded planner, tasi_shard.cuh): every band_rt tile rows are followed by one
     // DEAD tile row that is never scheduled; it holds the halo rows of the bands above and below it. 0 = no stack.
     int band_rt;
+    // fused multi-GPU mode (see "fused multi-GPU mode" below): nullptr = off
+    const struct FusedTopo *ft;
+    int *inbox;            // tiles parked here by OTHER ranks since the last phase boundary (this rank drains it)
+    int inbox_cap;
+    int fmode;             // fused launch: 0 relax (value-ordered), 1 invalidate (no order: everything parked is released)
 };
 
 // tile row `tx` of a band stack is a dead row (halo storage between two bands)
@@ -305,6 +310,272 @@ __device__ inline void drain_and_advance(const GridDesc &d, int *s_red, int *s_a
     }
 }
 
+// ---- fused multi-GPU mode ---------------------------------------------------------------------------------------------
+// One persistent solver per GPU, all running at the same time on the bands of ONE grid (tasi_shard.cuh), with no outer
+// iteration: a visit of a tile on a band border stores its changed boundary row straight into the halo row of the rank
+// that owns the band across the edge (peer-mapped memory over NVLink) and activates that rank's tiles with system-scope
+// atomics on ITS tile states, keys and work queue — the transfer is part of the tile visit, tile by tile. The value
+// order of the schedule is global: thresholds advance in lock-step. Rank 0's CTA 0 is the coordinator; it sees the grid
+// quiescent when `active` (the number of ranks with pending tiles, kept exact by +1 BEFORE any 0 -> 1 transition of a
+// rank's pending count and -1 AFTER any 1 -> 0) is 0, asks every rank for the lowest key of its pile (MIN), and answers
+// with the new threshold (RELEASE) or the end of the launch (DONE). Commands and replies are single words in each
+// other's memory; every rank's CTA 0 looks at its command word whenever it waits for a tile.
+constexpr int FUSED_MAX_RANKS = 16;
+constexpr int FOP_MIN = 1, FOP_RELEASE = 2, FOP_DONE = 3;
+
+struct FusedCtl {
+    int cmd;                    // (seq << 2) | op, written by the coordinator
+    int cmd_thr_bits;           // RELEASE: the new threshold
+    int seen_seq;               // seq of the last command this rank served (persists across launches)
+    int seq;                    // coordinator: last sequence number issued (persists across launches)
+    int active;                 // coordinator: ranks with pending tiles (+ pushes in flight)
+    int inbox_count;            // entries of this rank's inbox
+    unsigned long long rx;      // remote activations received (statistics)
+    unsigned long long tx;      // remote activations sent (statistics)
+    int ack[FUSED_MAX_RANKS];   // coordinator: ack[r] = seq of the last command rank r completed
+    int rmin[FUSED_MAX_RANKS];  // coordinator: rank r's reply to MIN (float bits)
+};
+
+struct FusedTopo {
+    int world, rank, parts, mode;
+    GridDesc nbr[2];                // [0] the rank holding the bands above ours, [1] below; pointers valid from this device
+    FusedCtl *fc[FUSED_MAX_RANKS];  // every rank's control block (peer-mapped)
+};
+
+__device__ __forceinline__ void fence_sys() { asm volatile("fence.acq_rel.sys;" ::: "memory"); }
+__device__ __forceinline__ int ld_sys(const int *p) { return *(const volatile int *) p; }
+
+// the pending count of this rank is about to leave / has just reached 0 (see `active` above)
+__device__ __forceinline__ void fused_rank_wakes(const GridDesc &d) { atomicAdd_system(&d.ft->fc[0]->active, 1); }
+__device__ __forceinline__ void fused_rank_idles(const GridDesc &d) { atomicAdd_system(&d.ft->fc[0]->active, -1); }
+
+// activate() on a tile of another rank `r` (its GridDesc, peer-mapped). `near` is judged by OUR threshold: thresholds
+// are global in this mode.
+__device__ inline void activate_remote(const GridDesc &d, const GridDesc &r, FusedCtl *rfc, int tile, int kbits, int dirbit) {
+    atomicMin_system(&r.key[tile], kbits);
+    const bool near = kbits < cur_thr_bits(d);
+    const int old = atomicOr_system(&r.state[tile], ST_DIRTY | (dirbit << ST_SHIFT));
+    const int st = old & ST_MASK;
+    bool push = false;
+    if (st == 0) {
+        if (near) push = true;
+        else {
+            atomicOr_system(&r.state[tile], ST_FAR);
+            const int slot = atomicAdd_system(&rfc->inbox_count, 1);
+            if (slot < r.inbox_cap) { r.inbox[slot] = tile; fence_sys(); }
+            else { atomicAnd_system(&r.state[tile], ~ST_FAR); push = true; }  // inbox full: run it now
+        }
+    } else if ((st & ST_FAR) && near) {
+        if (atomicAnd_system(&r.state[tile], ~ST_FAR) & ST_FAR) push = true;
+    }
+    if (push) {
+        fused_rank_wakes(d);  // BEFORE the count of the other rank can leave 0 ...
+        if (atomicAdd_system(&r.ctl->pending, 1) != 0) fused_rank_idles(d);  // ... it was awake already
+        const unsigned long long t = atomicAdd_system(&r.ctl->tail, 1ULL);
+        atomicExch_system(&r.queue[(unsigned) t & r.qmask], tile + 1);
+        atomicAdd_system(&rfc->rx, 1ULL);
+    }
+    atomicAdd(&d.ft->fc[d.ft->rank]->tx, 1ULL);
+}
+
+// lowest key of this rank's pile (all threads of the CTA; the inbox is moved into the pile first: the grid is quiescent)
+__device__ inline int fused_pile_min(const GridDesc &d, int *s_red, int tid) {
+    DevCtl *c = d.ctl;
+    FusedCtl *fc = d.ft->fc[d.ft->rank];
+    const int nthreads = blockDim.x;
+    const int cur = ld_sys(&c->far_sel);
+    const int nin = min(ld_sys(&fc->inbox_count), d.inbox_cap);
+    for (int i = tid; i < nin; i += nthreads) {
+        const int t = __ldcg(d.inbox + i);
+        if (ld_sys(&d.state[t]) & ST_FAR) {
+            const int slot = atomicAdd(&c->far_count[cur], 1);
+            if (slot < d.far_cap) d.far[cur * d.far_cap + slot] = t;
+            else if (atomicAnd(&d.state[t], ~ST_FAR) & ST_FAR) {  // pile full: run it with the next release
+                if (atomicAdd(&c->pending, 1) == 0) fused_rank_wakes(d);
+                const unsigned long long tk = atomicAdd(&c->tail, 1ULL);
+                atomicExch(&d.queue[(unsigned) tk & d.qmask], t + 1);
+            }
+        }
+    }
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) fc->inbox_count = 0;
+    const int n = min(ld_sys(&c->far_count[cur]), d.far_cap);
+    const int *src = d.far + cur * d.far_cap;
+    int m = INF_BITS;
+    const bool keyed = d.fmode == 0;  // the invalidate mode has no order (and no keys): any parked tile counts as 0
+    for (int i = tid; i < n; i += nthreads) {
+        const int t = __ldcg(src + i);
+        if (ld_sys(&d.state[t]) & ST_FAR) m = min(m, keyed ? ld_sys(&d.key[t]) : 0);
+    }
+    m = __reduce_min_sync(0xffffffffu, m);
+    if ((tid & 31) == 0) s_red[tid >> 5] = m;
+    __syncthreads();
+    m = s_red[0];
+    for (int w = 1; w < nthreads / 32; ++w) m = min(m, s_red[w]);
+    __syncthreads();
+    return m;
+}
+
+// new threshold: the parked tiles below it go to the queue (all threads of the CTA)
+__device__ inline void fused_pile_release(const GridDesc &d, int nthr, int tid) {
+    DevCtl *c = d.ctl;
+    const int nthreads = blockDim.x;
+    const int cur = ld_sys(&c->far_sel);
+    const int n = min(ld_sys(&c->far_count[cur]), d.far_cap);
+    const int *src = d.far + cur * d.far_cap;
+    if (tid == 0) {
+        fused_rank_wakes(d);
+        atomicAdd(&c->pending, 1);  // hold the count while tiles are being pushed
+        c->thr_bits = nthr;
+        c->far_count[cur ^ 1] = 0;
+        c->far_sel = cur ^ 1;  // parkings by the tiles pushed below go to the other list
+        atomicAdd(&c->phases, 1);
+        __threadfence();
+    }
+    __syncthreads();
+    int *dst = d.far + (cur ^ 1) * d.far_cap;
+    for (int i = tid; i < n; i += nthreads) {
+        const int t = __ldcg(src + i);
+        if (!(ld_sys(&d.state[t]) & ST_FAR)) continue;  // stale entry (tile was promoted)
+        if (ld_sys(&d.key[t]) < nthr || nthr == INF_BITS) {
+            if (atomicAnd(&d.state[t], ~ST_FAR) & ST_FAR) {
+                q_push(d, t);
+                atomicAdd(&c->pushes, 1ULL);
+            }
+        } else {
+            const int slot = atomicAdd(&c->far_count[cur ^ 1], 1);
+            if (slot < d.far_cap) dst[slot] = t;
+            else if (atomicAnd(&d.state[t], ~ST_FAR) & ST_FAR) q_push(d, t);
+        }
+    }
+    __syncthreads();
+    if (tid == 0) {
+        c->far_count[cur] = 0;
+        if (atomicSub(&c->pending, 1) == 1) fused_rank_idles(d);  // nothing released here
+    }
+}
+
+// wait until word `p` (written by another rank) equals `want`; false on watchdog
+__device__ inline bool fused_wait_eq(const GridDesc &d, const int *p, int want) {
+    const unsigned long long t0 = globaltimer_ns();
+    while (ld_sys(p) != want) {
+        if (ld_sys(&d.ctl->error) || globaltimer_ns() - t0 > d.ctl->timeout_ns) { q_fail(d); return false; }
+        __nanosleep(64);
+    }
+    return true;
+}
+
+// CTA 0 of every rank, whenever q_pop_fused returns -2: serve the coordinator's command (ranks > 0) or run one phase
+// boundary (rank 0). s_cmd: two shared ints.
+__device__ inline void fused_service(const GridDesc &d, int *s_red, int *s_cmd, int tid) {
+    const FusedTopo &ft = *d.ft;
+    FusedCtl *me = ft.fc[ft.rank], *co = ft.fc[0];
+    if (ft.rank == 0) {
+        int seq = 0;
+        if (tid == 0) {
+            seq = ++me->seq;
+            for (int r = 1; r < ft.world; ++r) { fence_sys(); *(volatile int *) &ft.fc[r]->cmd = (seq << 2) | FOP_MIN; }
+        }
+        int m = fused_pile_min(d, s_red, tid);
+        if (tid == 0) {
+            bool ok = true;
+            for (int r = 1; r < ft.world && ok; ++r) {
+                ok = fused_wait_eq(d, &me->ack[r], seq);
+                m = min(m, ld_sys(&me->rmin[r]));
+            }
+            int op = FOP_DONE, nthr = INF_BITS;
+            if (ok && m != INF_BITS) {
+                op = FOP_RELEASE;
+                if (d.fmode == 0 && d.delta > 0.0f) {
+                    nthr = __float_as_int(__int_as_float(m) + d.delta);
+                    if (nthr <= m) nthr = m + 1;  // delta lost to rounding: still let the lowest tile through
+                }
+            }
+            seq = ++me->seq;
+            for (int r = 1; r < ft.world; ++r) {
+                *(volatile int *) &ft.fc[r]->cmd_thr_bits = nthr;
+                fence_sys();
+                *(volatile int *) &ft.fc[r]->cmd = (seq << 2) | op;
+            }
+            s_cmd[0] = op; s_cmd[1] = nthr;
+            d.ctl->far_min_bits = m;
+        }
+        __syncthreads();
+        const int op = s_cmd[0], nthr = s_cmd[1];
+        if (op == FOP_RELEASE) {
+            fused_pile_release(d, nthr, tid);
+            if (tid == 0)
+                for (int r = 1; r < ft.world; ++r)
+                    if (!fused_wait_eq(d, &me->ack[r], seq)) break;
+        } else if (tid == 0) {
+            __threadfence();
+            atomicExch(&d.ctl->done, 1);
+        }
+        __syncthreads();
+        return;
+    }
+    if (tid == 0) {
+        const int cmd = ld_sys(&me->cmd);
+        fence_sys();
+        s_cmd[0] = cmd; s_cmd[1] = ld_sys(&me->cmd_thr_bits);
+    }
+    __syncthreads();
+    const int cmd = s_cmd[0], op = cmd & 3, seq = cmd >> 2;
+    if (op == FOP_MIN) {
+        const int m = fused_pile_min(d, s_red, tid);
+        if (tid == 0) { *(volatile int *) &co->rmin[ft.rank] = m; d.ctl->far_min_bits = m; }
+    } else if (op == FOP_RELEASE) {
+        fused_pile_release(d, s_cmd[1], tid);
+    } else if (tid == 0) {
+        __threadfence();
+        atomicExch(&d.ctl->done, 1);
+    }
+    __syncthreads();
+    if (tid == 0) {
+        me->seen_seq = seq;
+        fence_sys();
+        *(volatile int *) &co->ack[ft.rank] = seq;
+    }
+    __syncthreads();
+}
+
+// q_pop for CTA 0 in fused mode: also watches for the coordinator's command (rank 0: for the grid going quiescent).
+// *ticket == ~0: take a new ticket. Returns the tile, -1 (launch over) or -2 (call fused_service, then come back
+// with the same ticket).
+__device__ inline int q_pop_fused(const GridDesc &d, unsigned long long *ticket) {
+    const FusedTopo &ft = *d.ft;
+    FusedCtl *me = ft.fc[ft.rank];
+    if (*ticket == ~0ULL) *ticket = atomicAdd(&d.ctl->head, 1ULL);
+    volatile int *slot = &d.queue[(unsigned) *ticket & d.qmask];
+    volatile int *done = &d.ctl->done;
+    unsigned long long t0 = 0, tail0 = 0;
+    unsigned ns = 32;
+    for (;;) {
+        int v = *slot;
+        if (v != 0) {
+            *slot = 0;
+            *ticket = ~0ULL;
+            return v - 1;
+        }
+        if (*done) return -1;
+        if (ft.rank == 0) {
+            if (ld_sys(&me->active) == 0) return -2;
+        } else if ((ld_sys(&me->cmd) >> 2) != me->seen_seq) return -2;
+        if (t0 == 0) {
+            t0 = globaltimer_ns();
+            tail0 = *(volatile unsigned long long *) &d.ctl->tail;
+        } else if (globaltimer_ns() - t0 > d.ctl->timeout_ns) {
+            const unsigned long long tl = *(volatile unsigned long long *) &d.ctl->tail;
+            if (tl == tail0) { q_fail(d); return -1; }
+            tail0 = tl;
+            t0 = globaltimer_ns();
+        }
+        __nanosleep(ns);
+        if (ns < Q_SLEEP_MAX_NS) ns <<= 1;
+    }
+}
+
 // ---- in-tile relaxation: strips with a register copy of their neighbourhood ------------------------------------------
 // Thread t owns the 1x4 strip (row t>>3, columns 4*(t&7)..+3) of the staged tile and keeps, in registers, the 3x6
 // window of values around it as it last saw them. A round = reload the window from shared memory; if any of the
@@ -477,6 +748,9 @@ __global__ void __launch_bounds__(1024 / SW, SW == 4 ? 2 : 1) solver_kernel(Grid
     __shared__ int s_tile, s_inmask, s_again, s_adv;
     __shared__ int s_kmin[8];             // per neighbour direction: lowest changed value it will read (bits)
     __shared__ int s_red[MAX_WARPS];
+    __shared__ int s_cmd[2];              // fused mode: command being served by CTA 0
+    const bool fused = d.ft != nullptr;
+    unsigned long long ticket = ~0ULL;    // fused mode, CTA 0: the queue ticket it is waiting on
 
     const float INF = __int_as_float(0x7f800000);
     const int tid = threadIdx.x, lane = tid & 31;
@@ -487,7 +761,7 @@ __global__ void __launch_bounds__(1024 / SW, SW == 4 ? 2 : 1) solver_kernel(Grid
 
     // resumed band solve with nothing queued: arm_solver left one virtual pending tile for CTA 0 to retire, which
     // takes the count to 0 and starts the threshold advance
-    if (blockIdx.x == 0) {
+    if (blockIdx.x == 0 && !fused) {
         if (tid == 0) {
             s_adv = 0;
             if (*(volatile int *) &d.ctl->kick) {
@@ -500,7 +774,7 @@ __global__ void __launch_bounds__(1024 / SW, SW == 4 ? 2 : 1) solver_kernel(Grid
 
     for (;;) {
         if (tid == 0) {
-            int t = q_pop(d);
+            int t = (fused && blockIdx.x == 0) ? q_pop_fused(d, &ticket) : q_pop(d);
             if (t >= 0) {
                 // claim the tile: the word we take away carries the direction bits of every activation so far;
                 // their values were fenced before the bits were set, the fence below orders our loads after it
@@ -514,6 +788,10 @@ __global__ void __launch_bounds__(1024 / SW, SW == 4 ? 2 : 1) solver_kernel(Grid
         if (tid < 8) s_kmin[tid] = INF_BITS;
         __syncthreads();
         const int tile = s_tile;
+        if (tile == -2) {  // fused mode, CTA 0: a phase boundary / a command of the coordinator
+            fused_service(d, s_red, s_cmd, tid);
+            continue;
+        }
         if (tile < 0) break;
         c1 = clock64(); c_pop += c1 - c0; c0 = c1;
         const int tx = tile / d.TY, ty = tile - tx * d.TY;
@@ -602,6 +880,25 @@ __global__ void __launch_bounds__(1024 / SW, SW == 4 ? 2 : 1) solver_kernel(Grid
                     for (int j = 0; j < SW; ++j)
                         if ((chg >> j) & 1u) gp[j] = w[1][j + 1];
                 }
+                if (fused && (row == 0 || row == TS - 1)) {
+                    // fused mode: a band border row goes straight into the halo row of the rank across the edge
+                    const FusedTopo &ft = *d.ft;
+                    const int bp = d.band_rt + 1, bt = tx % bp, jb = tx / bp, gb = jb * ft.world + ft.rank;
+                    float *rp = nullptr;
+                    if (row == 0 && bt == 0 && gb > 0) {
+                        const int ju = ft.rank > 0 ? jb : jb - 1;  // the band above is the neighbour's band ju
+                        rp = ft.nbr[0].g + (int64_t) ((ju * bp + d.band_rt) * TS) * ft.nbr[0].gpitch;
+                    } else if (row == TS - 1 && bt == d.band_rt - 1 && gb + 1 < ft.parts) {
+                        const int jd = ft.rank < ft.world - 1 ? jb : jb + 1;
+                        rp = ft.nbr[1].g + ((int64_t) (jd * bp) * TS - 1) * ft.nbr[1].gpitch;
+                    }
+                    if (rp) {
+                        rp += y0 + col0;
+#pragma unroll
+                        for (int j = 0; j < SW; ++j)
+                            if ((chg >> j) & 1u) __stcg(rp + j, w[1][j + 1]);
+                    }
+                }
                 int kb = INF_BITS, kfirst = INF_BITS, klast = INF_BITS;
 #pragma unroll
                 for (int j = 0; j < SW; ++j)
@@ -628,7 +925,10 @@ __global__ void __launch_bounds__(1024 / SW, SW == 4 ? 2 : 1) solver_kernel(Grid
             __syncthreads();
             // the CTA's write-back (ordered by the barrier) before the flags below; the leaving thread sits in another
             // warp than the activating ones, so its atomics overlap theirs instead of following them
-            if (tid < 8 || tid == LEAVE_TID) fence_gpu();
+            if (tid < 8 || tid == LEAVE_TID) {
+                if (fused) fence_sys();
+                else fence_gpu();
+            }
 
             // activate the neighbours that read a changed border, one thread per direction
             // (0 N, 1 S, 2 W, 3 E, 4 NW, 5 NE, 6 SW, 7 SE); our north border is the south halo of the tile above
@@ -642,6 +942,19 @@ __global__ void __launch_bounds__(1024 / SW, SW == 4 ? 2 : 1) solver_kernel(Grid
                 const int nx = tx + dx, ny = ty + dy;
                 if (k != INF_BITS && nx >= 0 && nx < d.TX && ny >= 0 && ny < d.TY && !dead_tile_row(d, nx))
                     activate(d, nx * d.TY + ny, k, seen_as);
+                else if (fused && k != INF_BITS && dx != 0 && ny >= 0 && ny < d.TY) {
+                    // across a band edge: the tile belongs to a neighbour rank
+                    const FusedTopo &ft = *d.ft;
+                    const int bp = d.band_rt + 1, bt = tx % bp, jb = tx / bp, gb = jb * ft.world + ft.rank;
+                    if (dx < 0 && bt == 0 && gb > 0) {
+                        const int ju = ft.rank > 0 ? jb : jb - 1;
+                        activate_remote(d, ft.nbr[0], ft.fc[(ft.rank + ft.world - 1) % ft.world],
+                                        (ju * bp + d.band_rt - 1) * d.TY + ny, k, seen_as);
+                    } else if (dx > 0 && bt == d.band_rt - 1 && gb + 1 < ft.parts) {
+                        const int jd = ft.rank < ft.world - 1 ? jb : jb + 1;
+                        activate_remote(d, ft.nbr[1], ft.fc[(ft.rank + 1) % ft.world], (jd * bp) * d.TY + ny, k, seen_as);
+                    }
+                }
             }
             // ... while thread 32 leaves the tile (a neighbour may re-queue it at once: we no longer touch its values)
             if (tid == LEAVE_TID) {
@@ -671,7 +984,12 @@ __global__ void __launch_bounds__(1024 / SW, SW == 4 ? 2 : 1) solver_kernel(Grid
             c1 = clock64(); c_post += c1 - c0; c0 = c1;
         } while (again);
 
-        // the tile is no longer pending; whoever takes the count to 0 advances the threshold
+        // the tile is no longer pending; whoever takes the count to 0 advances the threshold (fused mode: tells the
+        // coordinator that this rank has gone idle; thresholds advance globally, fused_service)
+        if (fused) {
+            if (tid == 0 && atomicSub(&d.ctl->pending, 1) == 1) fused_rank_idles(d);
+            continue;
+        }
         if (tid == 0) s_adv = (atomicSub(&d.ctl->pending, 1) == 1) ? 1 : 0;
         drain_and_advance(d, s_red, &s_adv, tid);
     }

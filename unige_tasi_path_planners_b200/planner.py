@@ -387,6 +387,25 @@ class ShardedPlanner(GpuPlanner):
             raise TasiError(rc, "tasi_nccl_unique_id failed (libnccl.so.2 not found?)")
         return buf.raw
 
+    def set_fused(self, enabled=True):
+        """Fused mode (default on): boundary rows and activations go straight into the neighbour GPU's memory inside the
+        tile visits; off = exchange iterations (NCCL or peer reads)."""
+        self._check(self._L.tasi_shard_set_fused(self._h, int(bool(enabled))))
+
+    def connect_peers(self, dist, device):
+        """Multi-process form: all-gather the CUDA IPC handles of every rank (torch.distributed, any backend) and map the
+        neighbours' memory — after every set_map / synth_map. Without it the planner runs the NCCL iterations."""
+        import torch
+        n = self._L.tasi_shard_ipc_size()
+        mine = C.create_string_buffer(n)
+        self._check(self._L.tasi_shard_ipc_export(self._h, mine))
+        world = dist.get_world_size()
+        t = torch.frombuffer(bytearray(mine.raw), dtype=torch.uint8).to(device)
+        out = [torch.empty_like(t) for _ in range(world)]
+        dist.all_gather(out, t)
+        blob = b"".join(bytes(o.cpu().numpy().tobytes()) for o in out)
+        self._check(self._L.tasi_shard_ipc_import(self._h, C.create_string_buffer(blob, len(blob))))
+
     def shard_stats(self):
         s = _lib.ShardStats()
         self._check(self._L.tasi_shard_get_stats(self._h, C.byref(s)))

@@ -47,6 +47,8 @@ def measure_side(rank, world, local, side, steps, warmup, kind=_planner.FD, leve
     p = _planner.ShardedPlanner(kind, level, rank=rank, n_ranks=world, unique_id=uid, device=local)
     p.set_occupancy_threshold(1.0)
     p.synth_map(seed, side, side, 0, 10, start, goal)
+    if world > 1 and os.environ.get("TASI_SHARD_FUSED", "1") != "0":
+        p.connect_peers(dist, dev)  # CUDA IPC handles of every rank's arrays: the fused mode (else NCCL iterations)
     p.set_start(*start)
     p.set_goal(*goal)
     for _ in range(max(warmup, 1)):
@@ -108,9 +110,16 @@ def measure_side(rank, world, local, side, steps, warmup, kind=_planner.FD, leve
            "exchanges": int(exchanges), "solver_ms_max_rank": solver_ms / steps,
            "solver_share_of_wall": (solver_ms / steps) / wall_ms if wall_ms > 0 else None,
            "bands": ss["bands"], "bands_per_gpu": ss["bands_per_rank"], "rows_per_band": ss["rows_per_band"],
-           "collective": "ncclSend/ncclRecv of the packed boundary rows to the two ring neighbours + ncclAllReduce(max) of "
-                         "{halo lowered, -lowest parked value} per outer iteration, on the planner stream" if ss["nccl"]
-                         else "none (one rank)",
+           "mode": "fused" if ss["fused"] else ("nccl iterations" if ss["nccl"] else "one rank"),
+           "collective": ("none on the data path: a border tile's visit stores its boundary row into the neighbour rank's halo "
+                          "row (peer-mapped memory over NVLink, CUDA IPC) and activates that rank's tiles with system-scope "
+                          "atomics; thresholds advance globally through command words (rank 0 coordinates); NCCL only "
+                          "sums the checksum") if ss["fused"] and world > 1 else
+                         ("ncclSend/ncclRecv of the packed boundary rows to the two ring neighbours + ncclAllReduce(max) of "
+                          "{halo lowered, -lowest parked value} per outer iteration, on the planner stream" if ss["nccl"]
+                          else "none (one rank)"),
+           "remote_activations": ss["remote_activations"],
+           "busy_frac_min_max_rank": [ss["busy_frac_min_rank"], ss["busy_frac_max_rank"]],
            "tile_visits_per_tile": int(cnt[0]) / steps / max(int(cnt[1]), 1),
            "gpu_launches_per_plan": int(cnt[2]) / steps,
            "steps": steps, "verified": verified,

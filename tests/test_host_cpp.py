@@ -103,6 +103,30 @@ def test_plan_demo_matches_oracle(demo, oracle, kind, tmp_path):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("kind", ["fd", "mfd"])
+@pytest.mark.parametrize("devices", ["0,0", "0,0,0"])
+def test_plan_demo_over_several_ranks_equals_one_device(demo, kind, devices, tmp_path):
+    """GpuFieldDPlanner<1>(devices) — the sharded planner behind the same class — plans and replans the same field, walks
+    the same path and reports the same counters of the reference's interface as the one-device object."""
+    L, W, seed = 300, 210, 23
+    args = [kind, "1", str(L), str(W), str(seed), "--patch", "110", "50", "60", "44", "99"]
+    outs = []
+    for extra, tag in ((["--device", "0"], "one"), (["--devices", devices], "many")):
+        dump = str(tmp_path / tag)
+        r = subprocess.run([demo] + args + ["--dump", dump] + extra, capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr
+        outs.append(([json.loads(l) for l in r.stdout.splitlines()], dump))
+    (one, d1), (many, d2) = outs
+    for what, a, b in (("plan", one[0], many[0]), ("replan", one[1], many[1])):
+        assert np.array_equal(np.fromfile(d1 + "." + what, np.float32), np.fromfile(d2 + "." + what, np.float32))
+        assert np.array_equal(np.fromfile(d1 + "." + what + ".path", np.float32),
+                              np.fromfile(d2 + "." + what + ".path", np.float32))
+        for key in ("finite", "sum", "start_value", "start_interp_rhs", "path_points", "path_cost", "path_dist",
+                    "num_nodes_updated"):
+            assert a[key] == b[key], (what, key)
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("kind,level", [("fd", 1), ("fd", 0), ("mfd", 1), ("dfm", 1)])
 def test_reference_extractor_and_demo_loop_over_gpu_planner(kind, level):
     """The reference's own extractor + demo loop: CPU planner vs GPU planner class, same patches, step by step."""

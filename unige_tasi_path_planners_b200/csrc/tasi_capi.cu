@@ -19,6 +19,10 @@
 
 using namespace tasi;
 
+#ifndef TASI_COMPACT_DEFAULT
+#define TASI_COMPACT_DEFAULT 0
+#endif
+
 struct tasi_shard;
 static thread_local std::string g_create_err = "null planner";
 
@@ -174,20 +178,34 @@ void free_grid(tasi_planner *p) {
 }
 
 typedef void (*solver_fn)(GridDesc);
-template <int SW>
+template <int SW, int CMP>
 solver_fn pick_solver_sw(int kind, int mode) {
     switch (kind * 2 + mode) {
-        case TASI_FD * 2 + 0: return solver_kernel<TASI_KIND_FD, 0, SW>;
-        case TASI_FD * 2 + 1: return solver_kernel<TASI_KIND_FD, 1, SW>;
-        case TASI_DFM * 2 + 0: return solver_kernel<TASI_KIND_DFM, 0, SW>;
-        case TASI_DFM * 2 + 1: return solver_kernel<TASI_KIND_DFM, 1, SW>;
-        case TASI_MFD * 2 + 0: return solver_kernel<TASI_KIND_MFD, 0, SW>;
-        default: return solver_kernel<TASI_KIND_MFD, 1, SW>;
+        case TASI_FD * 2 + 0: return solver_kernel<TASI_KIND_FD, 0, SW, CMP>;
+        case TASI_FD * 2 + 1: return solver_kernel<TASI_KIND_FD, 1, SW, 0>;
+        case TASI_DFM * 2 + 0: return solver_kernel<TASI_KIND_DFM, 0, SW, CMP>;
+        case TASI_DFM * 2 + 1: return solver_kernel<TASI_KIND_DFM, 1, SW, 0>;
+        case TASI_MFD * 2 + 0: return solver_kernel<TASI_KIND_MFD, 0, SW, CMP>;
+        default: return solver_kernel<TASI_KIND_MFD, 1, SW, 0>;
     }
+}
+// How the relax visits evaluate: 0 strips (relax_tile), 1 compacted over the CTA (relax_tile_compact), 2 compacted
+// inside each warp (relax_tile_wcompact). TASI_COMPACT=0|1|2 overrides the per-planner default.
+inline int compact_mode(int kind) {
+    static const int env = [] {
+        const char *e = getenv("TASI_COMPACT");
+        return e ? atoi(e) : -1;
+    }();
+    if (env >= 0 && env <= 2) return env;
+    return kind == TASI_FD ? 1 : 0;
 }
 // strip = elements per thread of a tile row: 4 (256-thread CTAs, two per SM) or 2 (512-thread CTAs, one per SM)
 solver_fn pick_solver(int kind, int mode, int strip) {
-    return strip == 2 ? pick_solver_sw<2>(kind, mode) : pick_solver_sw<4>(kind, mode);
+    switch (compact_mode(kind)) {
+        case 2: return strip == 2 ? pick_solver_sw<2, 2>(kind, mode) : pick_solver_sw<4, 2>(kind, mode);
+        case 1: return strip == 2 ? pick_solver_sw<2, 1>(kind, mode) : pick_solver_sw<4, 1>(kind, mode);
+        default: return strip == 2 ? pick_solver_sw<2, 0>(kind, mode) : pick_solver_sw<4, 0>(kind, mode);
+    }
 }
 
 // (Re)allocate the device arrays for a map of `rows` x `W` cells. Margins: cost bytes 255, values INF.
@@ -339,6 +357,9 @@ int run_solver(tasi_planner *p, int mode, float *ms, bool resume = false, float 
     int rc = read_ctl(p, &h);
     if (rc != TASI_OK) return rc;
     CU_TRY(p, cudaEventElapsedTime(ms, p->ev0, p->ev1));
+#ifdef TASI_DEBUG_COMPACT
+    if (h.kick >= 100000) { p->err = "compact debug flag " + std::to_string(h.kick); return TASI_ERR_STATE; }
+#endif
     p->sv_far_sel = h.far_sel;
     p->sv_far_count[0] = std::min(h.far_count[0], p->far_cap);
     p->sv_far_count[1] = std::min(h.far_count[1], p->far_cap);

@@ -728,6 +728,212 @@ __device__ __forceinline__ int relax_tile(float *sg, const float *sc, int inmask
     return cnt_changed;
 }
 
+// ---- in-tile relaxation, compacted (CMP = 1) --------------------------------------------------------------------------
+// The strip relaxation above spends most of its issue slots on lanes that have nothing to do: a front crosses a tile
+// diagonally, so in a typical round ~18 % of the elements are dirty but every warp holds a few of them and runs the
+// whole SW-element evaluation (profiles/r01_ncu_solver_dfm4096_v12.txt: 19.8 of 32 lanes active). Here a
+// round is split: (1) every thread compares the window of its strip with its register copy, as before, and derives
+// WHICH of its elements have a changed neighbourhood; (2) the dirty elements of the whole tile are compacted into a
+// dense list in shared memory (warp prefix sum + one shared atomic per warp); (3) thread i evaluates list element i —
+// one element per thread, dense warps, Jacobi order. The owner of a strip learns what changed from the next round's
+// window comparison (which is also what records the elements to write back), so there are no per-element flags.
+// Two CTA barriers per round instead of one per 1-2 sweeps; the bet is on the issue slots.
+template <int KIND, int SW>
+__device__ __forceinline__ int relax_tile_compact(float *sg, const float *sc, unsigned short *s_list, int *s_n, int inmask,
+                                                  int row, int col0, int rlim, int clim, int pin_r, int pin_c,
+                                                  float (&w)[WIN_R][SW + 2], unsigned &chg, unsigned &iters,
+                                                  unsigned &evals, int *dbg) {
+    constexpr int WIN_C = SW + 2, NT = (TS * TS) / SW;
+    const int tid = threadIdx.x, lane = tid & 31;
+    unsigned live = 0;
+#pragma unroll
+    for (int j = 0; j < SW; ++j)
+        if (row < rlim && col0 + j < clim && !(row == pin_r && col0 + j == pin_c)) live |= 1u << j;
+    bool dirty0 = (inmask & IN_ALL) != 0;
+    dirty0 |= (inmask & (IN_N | IN_NW | IN_NE)) && row == 0;
+    dirty0 |= (inmask & (IN_S | IN_SW | IN_SE)) && row == TS - 1;
+    dirty0 |= (inmask & (IN_W | IN_NW | IN_SW)) && col0 == 0;
+    dirty0 |= (inmask & (IN_E | IN_NE | IN_SE)) && col0 == TS - SW;
+    const float *base = sg + row * GP + col0;  // window origin: element (row-1, col0-1)
+    int cnt_changed = 0;
+    chg = 0;
+    bool first = true;
+    for (;;) {
+        const int par = iters & 1;
+        // (1) what changed around my strip since I last looked
+        unsigned coldiff = 0;
+#pragma unroll
+        for (int a = 0; a < WIN_R; ++a)
+#pragma unroll
+            for (int b = 0; b < WIN_C; ++b) {
+                const float x = *(const volatile float *) (base + a * GP + b);
+                if (__float_as_int(x) != __float_as_int(w[a][b])) {
+                    coldiff |= 1u << b;
+                    if (a == 1 && b >= 1 && b <= SW && !first) chg |= 1u << (b - 1);  // one of mine was lowered
+                }
+                w[a][b] = x;
+            }
+        unsigned dmask = 0;
+        if (first) dmask = dirty0 ? (1u << SW) - 1u : 0u;
+        else {
+#pragma unroll
+            for (int j = 0; j < SW; ++j)
+                if ((coldiff >> j) & 7u) dmask |= 1u << j;
+        }
+        dmask &= live;
+        first = false;
+        // (2) compaction
+        const int my = __popc(dmask);
+        int incl = my;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += t;
+        }
+        const int wtot = __shfl_sync(0xffffffffu, incl, 31);
+        int wbase = 0;
+        if (lane == 31 && wtot) wbase = atomicAdd(&s_n[par], wtot);
+        wbase = __shfl_sync(0xffffffffu, wbase, 31);
+        int pos = wbase + incl - my;
+#pragma unroll
+        for (int j = 0; j < SW; ++j)
+            if ((dmask >> j) & 1u) s_list[pos++] = (unsigned short) (row * TS + col0 + j);
+        __syncthreads();
+        int n = *(volatile int *) &s_n[par];
+        if (n == 0) {
+            if (tid == 0) s_n[par ^ 1] = 0;  // last round's count: both counters are 0 when the next visit starts
+            break;
+        }
+#ifdef TASI_DEBUG_COMPACT
+        if (n > TS * TS || n < 0) { if (tid == 0) atomicExch(dbg, 100000 + n); n = TS * TS; }
+#endif
+        // (3) one element per thread
+        for (int i = tid; i < n; i += NT) {
+            int e = s_list[i];
+#ifdef TASI_DEBUG_COMPACT
+            if (e >= TS * TS) { atomicExch(dbg, 200000 + e); e &= TS * TS - 1; }
+#endif
+            const int r = e >> 5, c = e & 31;
+            const volatile float *wb = sg + r * GP + c;
+            Nbr8 nb;
+            nb.nw = wb[0]; nb.n = wb[1]; nb.ne = wb[2];
+            nb.w = wb[GP]; const float cur = wb[GP + 1]; nb.e = wb[GP + 2];
+            nb.sw = wb[2 * GP]; nb.s = wb[2 * GP + 1]; nb.se = wb[2 * GP + 2];
+            float v;
+            if (KIND == TASI_KIND_DFM) v = dfm_cell(nb, sc[r * CP + c]);
+            else {
+                const float tl = sc[r * CP + c], tr = sc[r * CP + c + 1], bl = sc[(r + 1) * CP + c], br = sc[(r + 1) * CP + c + 1];
+                v = (KIND == TASI_KIND_FD) ? fd_node(nb, tl, tr, bl, br) : mfd_node(nb, tl, tr, bl, br);
+            }
+            if (v < cur) {
+                sg[(r + 1) * GP + c + 1] = v;
+                ++cnt_changed;
+            }
+            ++evals;
+        }
+        if (tid == 0) s_n[par ^ 1] = 0;  // the next round's counter; nobody adds to it before the barrier below
+        __syncthreads();
+        ++iters;
+    }
+    return cnt_changed;
+}
+
+// ---- in-tile relaxation, compacted inside each warp (CMP = 2) ------------------------------------------------------------
+// As relax_tile_compact, but the dirty elements are compacted per WARP (a warp owns SW whole rows of the tile): ballot-free
+// prefix sum over the lanes, a per-warp list in shared memory, lane i evaluates the warp's i-th dirty element. No CTA
+// barrier is added (the round barrier stays the only one, and two sweeps still share it); what is given up against the
+// CTA-wide list is the balance between warps.
+template <int KIND, int SW>
+__device__ __forceinline__ int relax_tile_wcompact(float *sg, const float *sc, unsigned short *s_wl, int inmask, int row,
+                                                   int col0, int rlim, int clim, int pin_r, int pin_c,
+                                                   float (&w)[WIN_R][SW + 2], unsigned &chg, unsigned &iters,
+                                                   unsigned &evals) {
+    constexpr int WIN_C = SW + 2, WELEMS = 32 * SW;  // elements (= SW rows) per warp
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    unsigned short *wl = s_wl + warp * WELEMS;
+    const int wrow0 = warp * SW, lrow = row - wrow0;
+    unsigned live = 0;
+#pragma unroll
+    for (int j = 0; j < SW; ++j)
+        if (row < rlim && col0 + j < clim && !(row == pin_r && col0 + j == pin_c)) live |= 1u << j;
+    bool dirty0 = (inmask & IN_ALL) != 0;
+    dirty0 |= (inmask & (IN_N | IN_NW | IN_NE)) && row == 0;
+    dirty0 |= (inmask & (IN_S | IN_SW | IN_SE)) && row == TS - 1;
+    dirty0 |= (inmask & (IN_W | IN_NW | IN_SW)) && col0 == 0;
+    dirty0 |= (inmask & (IN_E | IN_NE | IN_SE)) && col0 == TS - SW;
+    const float *base = sg + row * GP + col0;
+    int cnt_changed = 0;
+    chg = 0;
+    bool first = true;
+    for (;;) {
+        bool stored_any = false;
+#pragma unroll 1
+        for (int rep = 0; rep < 2; ++rep) {
+            unsigned coldiff = 0;
+#pragma unroll
+            for (int a = 0; a < WIN_R; ++a)
+#pragma unroll
+                for (int b = 0; b < WIN_C; ++b) {
+                    const float x = *(const volatile float *) (base + a * GP + b);
+                    if (__float_as_int(x) != __float_as_int(w[a][b])) {
+                        coldiff |= 1u << b;
+                        if (a == 1 && b >= 1 && b <= SW && !first) chg |= 1u << (b - 1);
+                    }
+                    w[a][b] = x;
+                }
+            unsigned dmask = 0;
+            if (first) dmask = dirty0 ? (1u << SW) - 1u : 0u;
+            else {
+#pragma unroll
+                for (int j = 0; j < SW; ++j)
+                    if ((coldiff >> j) & 7u) dmask |= 1u << j;
+            }
+            dmask &= live;
+            first = false;
+            const int my = __popc(dmask);
+            int incl = my;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int t = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o) incl += t;
+            }
+            const int total = __shfl_sync(0xffffffffu, incl, 31);
+            if (total) {  // uniform over the warp
+                int pos = incl - my;
+#pragma unroll
+                for (int j = 0; j < SW; ++j)
+                    if ((dmask >> j) & 1u) wl[pos++] = (unsigned short) (lrow * TS + col0 + j);
+                __syncwarp();
+                for (int i = lane; i < total; i += 32) {
+                    const int e = wl[i], r = wrow0 + (e >> 5), c = e & 31;
+                    const volatile float *wb = sg + r * GP + c;
+                    Nbr8 nb;
+                    nb.nw = wb[0]; nb.n = wb[1]; nb.ne = wb[2];
+                    nb.w = wb[GP]; const float cur = wb[GP + 1]; nb.e = wb[GP + 2];
+                    nb.sw = wb[2 * GP]; nb.s = wb[2 * GP + 1]; nb.se = wb[2 * GP + 2];
+                    float v;
+                    if (KIND == TASI_KIND_DFM) v = dfm_cell(nb, sc[r * CP + c]);
+                    else {
+                        const float tl = sc[r * CP + c], tr = sc[r * CP + c + 1], bl = sc[(r + 1) * CP + c],
+                                    br = sc[(r + 1) * CP + c + 1];
+                        v = (KIND == TASI_KIND_FD) ? fd_node(nb, tl, tr, bl, br) : mfd_node(nb, tl, tr, bl, br);
+                    }
+                    if (v < cur) {
+                        sg[(r + 1) * GP + c + 1] = v;
+                        ++cnt_changed;
+                        stored_any = true;
+                    }
+                    ++evals;
+                }
+                __syncwarp();
+            }
+            ++iters;
+        }
+        if (!__syncthreads_or(stored_any)) break;
+    }
+    return cnt_changed;
+}
+
 // ---- the persistent solver kernel ------------------------------------------------------------------------------
 // Staging geometry: values are fetched as 16-byte vectors from column y0-4 (rows are 128-byte aligned and the
 // arrays carry GMARGIN columns of margin), 10 vectors cover columns y0-4..y0+35 of one row; costs likewise as
@@ -739,7 +945,8 @@ constexpr int C_ROWS_NODE = TS + 1, C_ROWS_CELL = TS;
 
 // SW = strip width: 4 (256 threads, two CTAs per SM) or 2 (512 threads, one CTA per SM: half the serial work per
 // thread in a round, for the node planners on grids whose front never feeds more than one CTA per SM anyway).
-template <int KIND, int MODE, int SW>
+// CMP = 1 / 2: the relax visits use relax_tile_compact / relax_tile_wcompact (MODE 0 only).
+template <int KIND, int MODE, int SW, int CMP = 0>
 __global__ void __launch_bounds__(1024 / SW, SW == 4 ? 2 : 1) solver_kernel(GridDesc d) {
     constexpr int NT = (TS * TS) / SW, WIN_C = SW + 2;
     constexpr int G_ITERS = (G_VECS + NT - 1) / NT, C_ITERS = (C_ROWS_NODE * GV_PER_ROW + NT - 1) / NT;
@@ -749,6 +956,10 @@ __global__ void __launch_bounds__(1024 / SW, SW == 4 ? 2 : 1) solver_kernel(Grid
     __shared__ int s_kmin[8];             // per neighbour direction: lowest changed value it will read (bits)
     __shared__ int s_red[MAX_WARPS];
     __shared__ int s_cmd[2];              // fused mode: command being served by CTA 0
+    __shared__ unsigned short s_list[CMP ? TS * TS : 1];  // compacted relaxation: the dirty elements of a round (CMP = 2:
+                                                          // one list of 32 * SW entries per warp)
+    __shared__ int s_n[2];                // ... and how many (two counters, alternating by round)
+    if (CMP && threadIdx.x == 0) s_n[0] = s_n[1] = 0;
     const bool fused = d.ft != nullptr;
     unsigned long long ticket = ~0ULL;    // fused mode, CTA 0: the queue ticket it is waiting on
 
@@ -863,8 +1074,15 @@ __global__ void __launch_bounds__(1024 / SW, SW == 4 ? 2 : 1) solver_kernel(Grid
             for (int a2 = 0; a2 < WIN_R; ++a2)
 #pragma unroll
                 for (int b2 = 0; b2 < WIN_C; ++b2) w[a2][b2] = 0.0f;
-            n_changed += relax_tile<KIND, MODE, SW>(sg, sc, s_inmask, row, col0, rlim, clim, pin_r, pin_c, d.inval_tol, w, chg,
-                                                it, ev);
+            if (CMP == 2 && MODE == 0)
+                n_changed += relax_tile_wcompact<KIND, SW>(sg, sc, s_list, s_inmask, row, col0, rlim, clim, pin_r, pin_c, w,
+                                                           chg, it, ev);
+            else if (CMP == 1 && MODE == 0)
+                n_changed += relax_tile_compact<KIND, SW>(sg, sc, s_list, s_n, s_inmask, row, col0, rlim, clim, pin_r, pin_c,
+                                                          w, chg, it, ev, &d.ctl->kick);
+            else
+                n_changed += relax_tile<KIND, MODE, SW>(sg, sc, s_inmask, row, col0, rlim, clim, pin_r, pin_c, d.inval_tol, w,
+                                                        chg, it, ev);
             n_iters += it;   // counted once per CTA below (every thread sees the same number of rounds)
             n_evals += ev;
             c1 = clock64(); c_relax += c1 - c0; c0 = c1;

@@ -215,6 +215,18 @@ class GpuReplanner {
         map.bind(h_, KIND == TASI_DFM);
 #endif
     }
+    // One grid over several GPUs (tasi_create_sharded): same members, same results; the element rows are cut into bands
+    // dealt out cyclically over `devices`, each GPU runs one persistent solver over its bands and the boundary rows
+    // travel through peer-mapped memory during the tile visits (include/tasi_gpu.h, csrc/tasi_shard.cuh).
+    explicit GpuReplanner(const std::vector<int> &devices) {
+        const int rc = devices.size() == 1 ? tasi_create(KIND, LEVEL, devices[0], &h_)
+                                           : tasi_create_sharded(KIND, LEVEL, devices.data(), (int) devices.size(), &h_);
+        if (rc != TASI_OK)
+            throw GpuError(rc, std::string("tasi_create_sharded failed: ") + tasi_last_error(nullptr));
+#ifndef TASI_WITH_REFERENCE_TYPES
+        map.bind(h_, KIND == TASI_DFM);
+#endif
+    }
     ~GpuReplanner() { tasi_destroy(h_); }
     GpuReplanner(const GpuReplanner &) = delete;
     GpuReplanner &operator=(const GpuReplanner &) = delete;

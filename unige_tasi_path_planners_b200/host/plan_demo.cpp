@@ -3,6 +3,7 @@
 // set_map, set_start, set_goal, step; then patch_map + set_start + step for a replan.
 //
 //   plan_demo <fd|dfm|mfd> <level> <length> <width> <seed> [--patch x y h w pseed] [--dump FILE] [--device N]
+//             [--devices 0,1,...]     the same planner object over several GPUs (the sharded planner of the C ABI)
 //
 // The map is the deterministic synthetic grid of SURVEY.md 8(d) (same generator as synth.py and the CUDA
 // synth kernel). Prints one JSON line per step with the counters and a checksum of the field; --dump writes
@@ -72,14 +73,14 @@ void report(Planner &pl, const char *what, const std::string &dump) {
 
 template <typename Planner>
 int run(int length, int width, uint64_t seed, bool patch, int px, int py, int ph, int pw, uint64_t pseed,
-        const std::string &dump, int device) {
+        const std::string &dump, const std::vector<int> &devices) {
     std::shared_ptr<uint8_t> data(new uint8_t[(size_t) length * width], std::default_delete<uint8_t[]>());
     synth(data.get(), seed, length, width, 10);
     const tasi_host::Position start(5.0f, 5.0f), goal((float) (length - 6), (float) (width - 6));
     clear_block(data.get(), length, width, 5, 5);
     clear_block(data.get(), length, width, length - 6, width - 6);
 
-    Planner planner(device);
+    Planner planner(devices);
     if (planner.step() != LOOP_FAILURE_NO_GRAPH) return 2;  // ReplannerBase.h:44
     planner.reset();
     planner.set_occupancy_threshold(1);
@@ -110,7 +111,7 @@ int run(int length, int width, uint64_t seed, bool patch, int px, int py, int ph
 int main(int argc, char **argv) {
     if (argc < 6) {
         fprintf(stderr, "usage: %s <fd|dfm|mfd> <level> <length> <width> <seed> [--patch x y h w pseed] [--dump FILE] "
-                        "[--device N]\n", argv[0]);
+                        "[--device N | --devices 0,1,...]\n", argv[0]);
         return 64;
     }
     const std::string kind = argv[1];
@@ -120,6 +121,7 @@ int main(int argc, char **argv) {
     int px = 0, py = 0, ph = 0, pw = 0, device = 0;
     uint64_t pseed = 0;
     std::string dump;
+    std::vector<int> devices;
     for (int i = 6; i < argc; ++i) {
         if (!strcmp(argv[i], "--patch") && i + 5 < argc) {
             patch = true;
@@ -128,9 +130,16 @@ int main(int argc, char **argv) {
             i += 5;
         } else if (!strcmp(argv[i], "--dump") && i + 1 < argc) dump = argv[++i];
         else if (!strcmp(argv[i], "--device") && i + 1 < argc) device = atoi(argv[++i]);
+        else if (!strcmp(argv[i], "--devices") && i + 1 < argc) {
+            for (const char *c = argv[++i]; *c;) {
+                devices.push_back((int) strtol(c, (char **) &c, 10));
+                if (*c == ',') ++c;
+            }
+        }
     }
+    if (devices.empty()) devices.push_back(device);
     try {
-#define RUN(P) return run<P>(length, width, seed, patch, px, py, ph, pw, pseed, dump, device)
+#define RUN(P) return run<P>(length, width, seed, patch, px, py, ph, pw, pseed, dump, devices)
         if (kind == "fd") { if (level == 0) RUN(GpuFieldDPlanner<0>); else RUN(GpuFieldDPlanner<1>); }
         if (kind == "dfm") { if (level == 0) RUN(GpuDFMPlanner<0>); else RUN(GpuDFMPlanner<1>); }
         if (kind == "mfd") {

@@ -222,7 +222,8 @@ class GpuReplanner {
         const int rc = devices.size() == 1 ? tasi_create(KIND, LEVEL, devices[0], &h_)
                                            : tasi_create_sharded(KIND, LEVEL, devices.data(), (int) devices.size(), &h_);
         if (rc != TASI_OK)
-            throw GpuError(rc, std::string("tasi_create_sharded failed: ") + tasi_last_error(nullptr));
+            throw GpuError(rc, std::string(devices.size() == 1 ? "tasi_create" : "tasi_create_sharded") + " failed: " +
+                                   tasi_last_error(nullptr) + " (no CUDA device or library? this path has no CPU fallback)");
 #ifndef TASI_WITH_REFERENCE_TYPES
         map.bind(h_, KIND == TASI_DFM);
 #endif

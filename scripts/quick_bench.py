@@ -6,9 +6,11 @@ import time
 sys.path.insert(0, __file__.rsplit("/", 2)[0])
 from unige_tasi_path_planners_b200 import PLANNERS, synth  # noqa: E402
 
+import os  # noqa: E402
 sizes = [int(a) for a in sys.argv[1:]] or [1024, 4096]
+kinds = [int(k) for k in os.environ.get("QUICK_KINDS", "1,2,0").split(",")]
 for N in sizes:
-    for kind in (1, 2, 0):
+    for kind in kinds:
         p = PLANNERS[kind](PLANNERS[kind].max_level)
         p.set_occupancy_threshold(1.0)
         start, goal = synth.default_endpoints(N, N)

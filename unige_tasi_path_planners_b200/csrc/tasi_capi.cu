@@ -12,6 +12,8 @@
 #include <string>
 #include <vector>
 
+#include <cuda.h>  // CUtensorMap (types only: the driver entry point is looked up through the runtime, no -lcuda)
+
 #include "../../include/tasi_gpu.h"
 #include "tasi_solver.cuh"
 #include "tasi_extract.cuh"
@@ -69,6 +71,7 @@ struct tasi_planner {
     float delta_factor = 2.0f;  // width of the value band per threshold advance, in tiles of mean cost
     bool delta_auto = true;     // ... widened on small grids (band_width()), unless TASI_DELTA_FACTOR fixes it
     DevCtl *ctl = nullptr;
+    TmaMaps tm{};            // the two CUtensorMap of the TMA-staged solver instances (TASI_TMA=1), else zero
     float *stage = nullptr;  // 2 x EY receive rows (band mode)
     uint8_t *patch_buf = nullptr, *chg_buf = nullptr;
     size_t patch_cap = 0;
@@ -177,7 +180,7 @@ void free_grid(tasi_planner *p) {
     p->stage = nullptr;
 }
 
-typedef void (*solver_fn)(GridDesc);
+typedef void (*solver_fn)(GridDesc, TmaMaps);
 template <int SW, int CMP>
 solver_fn pick_solver_sw(int kind, int mode) {
     switch (kind * 2 + mode) {
@@ -199,13 +202,68 @@ inline int compact_mode(int kind) {
     if (env >= 0 && env <= 2) return env;
     return kind == TASI_FD ? 1 : 0;
 }
+// TASI_TMA=1: the relax instances stage their tiles with cp.async.bulk.tensor.2d instead of vector loads (strips only;
+// measured alternative, profiles/r02_tma_staging.txt)
+inline bool tma_mode() {
+    static const bool on = [] {
+        const char *e = getenv("TASI_TMA");
+        return e && atoi(e) == 1;
+    }();
+    return on;
+}
+template <int SW>
+solver_fn pick_solver_tma(int kind) {
+    switch (kind) {
+        case TASI_FD: return solver_kernel<TASI_KIND_FD, 0, SW, 0, 1>;
+        case TASI_DFM: return solver_kernel<TASI_KIND_DFM, 0, SW, 0, 1>;
+        default: return solver_kernel<TASI_KIND_MFD, 0, SW, 0, 1>;
+    }
+}
 // strip = elements per thread of a tile row: 4 (256-thread CTAs, two per SM) or 2 (512-thread CTAs, one per SM)
 solver_fn pick_solver(int kind, int mode, int strip) {
+    if (tma_mode() && mode == 0) return strip == 2 ? pick_solver_tma<2>(kind) : pick_solver_tma<4>(kind);
     switch (compact_mode(kind)) {
         case 2: return strip == 2 ? pick_solver_sw<2, 2>(kind, mode) : pick_solver_sw<4, 2>(kind, mode);
         case 1: return strip == 2 ? pick_solver_sw<2, 1>(kind, mode) : pick_solver_sw<4, 1>(kind, mode);
         default: return strip == 2 ? pick_solver_sw<2, 0>(kind, mode) : pick_solver_sw<4, 0>(kind, mode);
     }
+}
+
+// The two tensor maps of the TMA-staged solver instances: the padded value array as a 2-D float32 tensor with a 36 x 34
+// box (a tile's 34 x 34 window, inner extent rounded up to 16 bytes), the padded cost array as a uint8 tensor with a
+// 48 x 33 box. cuTensorMapEncodeTiled is a driver entry point; it is taken from the runtime (cudaGetDriverEntryPoint).
+int make_tensor_maps(tasi_planner *p) {
+    typedef CUresult (*encode_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                  const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    void *fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    CU_TRY(p, cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
+    if (!fn || qres != cudaDriverEntryPointSuccess) return fail(p, TASI_ERR_CUDA, "cuTensorMapEncodeTiled not available");
+    alignas(64) CUtensorMap m[2];
+    const cuuint32_t estr[2] = {1, 1};
+    {
+        const cuuint64_t dims[2] = {(cuuint64_t) p->gpitch, (cuuint64_t) p->g_rows};
+        const cuuint64_t strides[1] = {(cuuint64_t) p->gpitch * sizeof(float)};
+        const cuuint32_t box[2] = {(cuuint32_t) TMA_GW, (cuuint32_t) (TS + 2)};
+        const CUresult r = ((encode_fn) fn)(&m[0], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, p->g_base, dims, strides, box, estr,
+                                            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                                            CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) return fail(p, TASI_ERR_CUDA, "cuTensorMapEncodeTiled (values) failed");
+    }
+    {
+        const cuuint64_t dims[2] = {(cuuint64_t) p->cpitch, (cuuint64_t) p->g_rows};
+        const cuuint64_t strides[1] = {(cuuint64_t) p->cpitch};
+        const cuuint32_t box[2] = {(cuuint32_t) TMA_CW, (cuuint32_t) (TS + 1)};
+        const CUresult r = ((encode_fn) fn)(&m[1], CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, p->c_base, dims, strides, box, estr,
+                                            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                                            CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) return fail(p, TASI_ERR_CUDA, "cuTensorMapEncodeTiled (costs) failed");
+    }
+    static_assert(sizeof(CUtensorMap) == sizeof(p->tm.g), "CUtensorMap is 128 bytes");
+    memcpy(p->tm.g, &m[0], sizeof(CUtensorMap));
+    memcpy(p->tm.c, &m[1], sizeof(CUtensorMap));
+    return TASI_OK;
 }
 
 // (Re)allocate the device arrays for a map of `rows` x `W` cells. Margins: cost bytes 255, values INF.
@@ -225,6 +283,7 @@ int alloc_grid_arrays(tasi_planner *p, int EY, int nt, unsigned q) {
     CU_TRY(p, cudaMemsetAsync(p->state, 0, sizeof(int) * nt, p->stream));
     CU_TRY(p, cudaMemsetAsync(p->queue, 0, sizeof(int) * q, p->stream));
     CU_TRY(p, cudaMemsetAsync(p->seed, 0, nt, p->stream));
+    if (tma_mode()) return make_tensor_maps(p);
     return TASI_OK;
 }
 
@@ -350,7 +409,7 @@ int run_solver(tasi_planner *p, int mode, float *ms, bool resume = false, float 
     enqueue_seeds_kernel<<<std::min((nt + 255) / 256, 1024), 256, 0, p->stream>>>(d, ordered);
     arm_solver_kernel<<<1, 1, 0, p->stream>>>(d);
     const int nblocks = (p->max_blocks > 0 && p->max_blocks < p->solver_blocks) ? p->max_blocks : p->solver_blocks;
-    pick_solver(p->kind, mode, p->strip)<<<nblocks, TS * TS / p->strip, 0, p->stream>>>(d);
+    pick_solver(p->kind, mode, p->strip)<<<nblocks, TS * TS / p->strip, 0, p->stream>>>(d, p->tm);
     CU_TRY(p, cudaGetLastError());
     CU_TRY(p, cudaEventRecord(p->ev1, p->stream));
     DevCtl h;

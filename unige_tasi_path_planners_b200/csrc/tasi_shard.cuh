@@ -483,7 +483,7 @@ int shard_fused_run(tasi_shard *s, int mode) {
         enqueue_seeds_kernel<<<std::min((nt + 255) / 256, 1024), 256, 0, p->stream>>>(d, 1);
         const int cap = s->max_blocks > 0 ? s->max_blocks : p->max_blocks;
         const int nblocks = (cap > 0 && cap < p->solver_blocks) ? cap : p->solver_blocks;
-        pick_solver(p->kind, mode, p->strip)<<<nblocks, TS * TS / p->strip, 0, p->stream>>>(d);
+        pick_solver(p->kind, mode, p->strip)<<<nblocks, TS * TS / p->strip, 0, p->stream>>>(d, p->tm);
         SH_TRY(s, cudaGetLastError());
     }
     int rc = shard_sync_all(s);
@@ -723,7 +723,7 @@ int shard_launch_solver(tasi_shard *s, ShardMember &m, int mode) {
     arm_solver_kernel<<<1, 1, 0, p->stream>>>(d);
     const int cap = s->max_blocks > 0 ? s->max_blocks : p->max_blocks;
     const int nblocks = (cap > 0 && cap < p->solver_blocks) ? cap : p->solver_blocks;
-    pick_solver(p->kind, mode, p->strip)<<<nblocks, TS * TS / p->strip, 0, p->stream>>>(d);
+    pick_solver(p->kind, mode, p->strip)<<<nblocks, TS * TS / p->strip, 0, p->stream>>>(d, p->tm);
     SH_TRY(s, cudaGetLastError());
     return TASI_OK;
 }

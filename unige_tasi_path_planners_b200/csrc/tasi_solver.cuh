@@ -103,6 +103,14 @@ struct GridDesc {
     int fmode;             // fused launch: 0 relax (value-ordered), 1 invalidate (no order: everything parked is released)
 };
 
+// TMA staging (solver instances with TMA = 1, TASI_TMA=1): the two CUtensorMap (128 opaque bytes each) the kernel takes
+// as a __grid_constant__ parameter: g = the padded value array (float32, box 36 x 34), c = the padded cost array (uint8,
+// box 48 x 33). All-zero for the instances that stage with vector loads.
+struct TmaMaps {
+    alignas(64) unsigned long long g[16];
+    alignas(64) unsigned long long c[16];
+};
+
 // tile row `tx` of a band stack is a dead row (halo storage between two bands)
 __device__ __forceinline__ bool dead_tile_row(const GridDesc &d, int tx) {
     return d.band_rt > 0 && (tx % (d.band_rt + 1)) == d.band_rt;
@@ -934,6 +942,37 @@ __device__ __forceinline__ int relax_tile_wcompact(float *sg, const float *sc, u
     return cnt_changed;
 }
 
+// ---- TMA staging (measured alternative, TASI_TMA=1) ----------------------------------------------------------------------
+// The tile's 34 x 34 value window and its 33 x 33 cost window are boxes of two 2-D tensor maps over the padded arrays
+// (rows are 128-byte multiples, so any element coordinate is a legal box origin): one elected thread issues
+// cp.async.bulk.tensor.2d for each, the CTA waits on an mbarrier for the bytes, then re-pitches the landing buffers into
+// the conflict-free pitch-35 arrays the relaxation reads (the inner box extent must be a multiple of 16 bytes: 36 floats
+// / 48 bytes; with that pitch the strip windows would collide four ways). Values written by other CTAs reach L2 through
+// the generic proxy; the issuing thread orders them before its bulk read with fence.proxy.async.
+constexpr int TMA_GW = 36, TMA_CW = 48;  // landing pitches: floats per value row, bytes per cost row
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t) __cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t *bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+    uint32_t ok = 0;
+    const uint32_t a = smem_u32(bar);
+    do {
+        asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}"
+                     : "=r"(ok) : "r"(a), "r"(parity) : "memory");
+    } while (!ok);
+}
+__device__ __forceinline__ void tma_load_2d(void *dst, const void *tmap, uint64_t *bar, int c0, int c1) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+                 ::"r"(smem_u32(dst)), "l"(tmap), "r"(smem_u32(bar)), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async;" ::: "memory"); }
+
 // ---- the persistent solver kernel ------------------------------------------------------------------------------
 // Staging geometry: values are fetched as 16-byte vectors from column y0-4 (rows are 128-byte aligned and the
 // arrays carry GMARGIN columns of margin), 10 vectors cover columns y0-4..y0+35 of one row; costs likewise as
@@ -946,8 +985,9 @@ constexpr int C_ROWS_NODE = TS + 1, C_ROWS_CELL = TS;
 // SW = strip width: 4 (256 threads, two CTAs per SM) or 2 (512 threads, one CTA per SM: half the serial work per
 // thread in a round, for the node planners on grids whose front never feeds more than one CTA per SM anyway).
 // CMP = 1 / 2: the relax visits use relax_tile_compact / relax_tile_wcompact (MODE 0 only).
-template <int KIND, int MODE, int SW, int CMP = 0>
-__global__ void __launch_bounds__(1024 / SW, SW == 4 ? 2 : 1) solver_kernel(GridDesc d) {
+// TMA = 1: the windows are staged by cp.async.bulk.tensor.2d (see "TMA staging" above) instead of vector loads.
+template <int KIND, int MODE, int SW, int CMP = 0, int TMA = 0>
+__global__ void __launch_bounds__(1024 / SW, SW == 4 ? 2 : 1) solver_kernel(GridDesc d, const __grid_constant__ TmaMaps tm) {
     constexpr int NT = (TS * TS) / SW, WIN_C = SW + 2;
     constexpr int G_ITERS = (G_VECS + NT - 1) / NT, C_ITERS = (C_ROWS_NODE * GV_PER_ROW + NT - 1) / NT;
     __shared__ float sg[(TS + 2) * GP];   // values, rows/cols -1..32
@@ -959,6 +999,14 @@ __global__ void __launch_bounds__(1024 / SW, SW == 4 ? 2 : 1) solver_kernel(Grid
     __shared__ unsigned short s_list[CMP ? TS * TS : 1];  // compacted relaxation: the dirty elements of a round (CMP = 2:
                                                           // one list of 32 * SW entries per warp)
     __shared__ int s_n[2];                // ... and how many (two counters, alternating by round)
+    __shared__ __align__(128) float s_land[TMA ? (TS + 2) * TMA_GW : 1];        // TMA landing buffers
+    __shared__ __align__(128) unsigned char s_cland[TMA ? (TS + 1) * TMA_CW : 16];
+    __shared__ __align__(8) uint64_t s_bar;
+    unsigned tma_phase = 0;
+    if (TMA) {
+        if (threadIdx.x == 0) mbar_init(&s_bar, 1);
+        __syncthreads();
+    }
     if (CMP && threadIdx.x == 0) s_n[0] = s_n[1] = 0;
     const bool fused = d.ft != nullptr;
     unsigned long long ticket = ~0ULL;    // fused mode, CTA 0: the queue ticket it is waiting on
@@ -1015,17 +1063,42 @@ __global__ void __launch_bounds__(1024 / SW, SW == 4 ? 2 : 1) solver_kernel(Grid
         constexpr int c_r0 = (KIND == TASI_KIND_DFM) ? 0 : -1;  // first cost row / column relative to the tile
         constexpr int c_rows = (KIND == TASI_KIND_DFM) ? C_ROWS_CELL : C_ROWS_NODE;
         uchar4 cv[C_ITERS];
+        if (!TMA) {
 #pragma unroll
-        for (int k = 0; k < C_ITERS; ++k) {
-            const int i = tid + k * NT;
-            const int r = i / GV_PER_ROW, v = i - r * GV_PER_ROW;
-            if (i < c_rows * GV_PER_ROW)
-                cv[k] = __ldg((const uchar4 *) (d.cost + (int64_t) (x0 + c_r0 + r) * d.cpitch + (y0 - 4 + 4 * v)));
+            for (int k = 0; k < C_ITERS; ++k) {
+                const int i = tid + k * NT;
+                const int r = i / GV_PER_ROW, v = i - r * GV_PER_ROW;
+                if (i < c_rows * GV_PER_ROW)
+                    cv[k] = __ldg((const uchar4 *) (d.cost + (int64_t) (x0 + c_r0 + r) * d.cpitch + (y0 - 4 + 4 * v)));
+            }
         }
         bool first = true;
 
         bool again;
         do {
+            if (TMA) {
+                // coordinates in the padded arrays: element (ex, ey) sits at row ex + 1, column GMARGIN + ey
+                if (tid == 0) {
+                    fence_proxy_async();
+                    mbar_expect_tx(&s_bar, (unsigned) ((TS + 2) * TMA_GW * 4 + (first ? (TS + 1) * TMA_CW : 0)));
+                    tma_load_2d(s_land, &tm.g, &s_bar, GMARGIN + y0 - 1, x0);
+                    if (first) tma_load_2d(s_cland, &tm.c, &s_bar, GMARGIN + y0 + c_r0, x0 + c_r0 + 1);
+                }
+                mbar_wait(&s_bar, tma_phase);
+                tma_phase ^= 1u;
+                for (int i = tid; i < (TS + 2) * (TS + 2); i += NT) {
+                    const int r = i / (TS + 2), c = i - r * (TS + 2);
+                    sg[r * GP + c] = s_land[r * TMA_GW + c];
+                }
+                if (first) {
+                    first = false;
+                    for (int i = tid; i < c_rows * c_rows; i += NT) {
+                        const int r = i / c_rows, c = i - r * c_rows;
+                        const int b = s_cland[r * TMA_CW + c];
+                        sc[r * CP + c] = (b >= d.thr) ? INF : (float) b;
+                    }
+                }
+            } else {
             // stage values + halo ring; L1 is bypassed (other CTAs write these lines)
             float4 gv[G_ITERS];
 #pragma unroll
@@ -1063,6 +1136,7 @@ __global__ void __launch_bounds__(1024 / SW, SW == 4 ? 2 : 1) solver_kernel(Grid
                         if (c >= 0 && c < TS + 2) sg[r * GP + c] = ff[e];
                     }
                 }
+            }
             }
             __syncthreads();
             ++n_visits;

@@ -31,6 +31,7 @@ static thread_local std::string g_create_err = "null planner";
 struct tasi_planner {
     tasi_shard *shard = nullptr;  // set on the handle of a sharded planner (tasi_shard.cuh): every entry point forwards
     int band_rt = 0;              // > 0: this grid is a stack of row bands of band_rt tile rows (a member of a shard)
+    int shard_world = 1;          // ... of a grid spread over this many GPUs
     const FusedTopo *ft = nullptr;  // fused multi-GPU mode (device pointer; tasi_shard.cuh), nullptr = off
     int *inbox = nullptr;
     int inbox_cap = 0;
@@ -124,7 +125,12 @@ inline bool node_based(const tasi_planner *p) { return p->kind != TASI_DFM; }
 inline float band_width(const tasi_planner *p) {
     float f = p->delta_factor;
     if (p->delta_auto && f > 0.0f && !p->focus && !p->open_top && !p->open_bottom) {
-        const double nt = std::max(1.0, (double) p->TX * (double) p->TY);
+        // a member of a sharded grid holds 1/world of the tiles and sees 1/world of the front of the WHOLE grid (its
+        // length goes with the square root of world x local tiles): the single-GPU grid with the same front per GPU has
+        // local tiles / world tiles (TASI_SHARD_DELTA_RULE=0: the local tile count, as before)
+        static const bool shard_rule = [] { const char *e = getenv("TASI_SHARD_DELTA_RULE"); return !e || atoi(e) != 0; }();
+        double nt = std::max(1.0, (double) p->TX * (double) p->TY);
+        if (shard_rule && p->shard_world > 1) nt = std::max(1.0, nt / (double) p->shard_world);
         f = (float) std::min(6.0, std::max(2.0, 2.0 + 0.5 * std::log2(262144.0 / nt)));
     }
     return f * (float) TS * p->mean_cost;
@@ -229,8 +235,8 @@ solver_fn pick_solver(int kind, int mode, int strip) {
     }
 }
 
-// The two tensor maps of the TMA-staged solver instances: the padded value array as a 2-D float32 tensor with a 36 x 34
-// box (a tile's 34 x 34 window, inner extent rounded up to 16 bytes), the padded cost array as a uint8 tensor with a
+// The two tensor maps of the TMA-staged solver instances: the padded value array as a 2-D float32 tensor with a 40 x 34
+// box (a tile's 34 x 34 window from the 16-byte aligned column left of it), the padded cost array as a uint8 tensor with a
 // 48 x 33 box. cuTensorMapEncodeTiled is a driver entry point; it is taken from the runtime (cudaGetDriverEntryPoint).
 int make_tensor_maps(tasi_planner *p) {
     typedef CUresult (*encode_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,

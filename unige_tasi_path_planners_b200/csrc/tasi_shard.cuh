@@ -383,6 +383,7 @@ int shard_layout(tasi_shard *s, int W, int L) {
         SH_TRY(s, cudaSetDevice(m.device));
         p->thr = s->thr;
         p->band_rt = s->RT;
+        p->shard_world = s->world;
         int rc = alloc_grid_dims(p, W, EX, EX, EY);
         if (rc != TASI_OK) return sh_sub(s, m, rc);
         if (same && m.xbuf) continue;

@@ -104,7 +104,7 @@ struct GridDesc {
 };
 
 // TMA staging (solver instances with TMA = 1, TASI_TMA=1): the two CUtensorMap (128 opaque bytes each) the kernel takes
-// as a __grid_constant__ parameter: g = the padded value array (float32, box 36 x 34), c = the padded cost array (uint8,
+// as a __grid_constant__ parameter: g = the padded value array (float32, box 40 x 34), c = the padded cost array (uint8,
 // box 48 x 33). All-zero for the instances that stage with vector loads.
 struct TmaMaps {
     alignas(64) unsigned long long g[16];
@@ -944,12 +944,14 @@ __device__ __forceinline__ int relax_tile_wcompact(float *sg, const float *sc, u
 
 // ---- TMA staging (measured alternative, TASI_TMA=1) ----------------------------------------------------------------------
 // The tile's 34 x 34 value window and its 33 x 33 cost window are boxes of two 2-D tensor maps over the padded arrays
-// (rows are 128-byte multiples, so any element coordinate is a legal box origin): one elected thread issues
-// cp.async.bulk.tensor.2d for each, the CTA waits on an mbarrier for the bytes, then re-pitches the landing buffers into
-// the conflict-free pitch-35 arrays the relaxation reads (the inner box extent must be a multiple of 16 bytes: 36 floats
-// / 48 bytes; with that pitch the strip windows would collide four ways). Values written by other CTAs reach L2 through
+// (rows are 128-byte multiples): one elected thread issues cp.async.bulk.tensor.2d for each, the CTA waits on an mbarrier
+// for the bytes, then re-pitches the landing buffers into the conflict-free pitch-35 arrays the relaxation reads. The
+// inner box origin must be 16-byte aligned (an unaligned inner coordinate raises "illegal instruction" on sm_100a,
+// scripts/probes/tma_probe.cu) and the inner extent a multiple of 16 bytes, so the boxes start at column y0 - 4 (values,
+// 40 floats) and y0 - 16 (costs, 48 bytes), as the vector loads do; with pitch 40 the strip windows would collide. Values written by other CTAs reach L2 through
 // the generic proxy; the issuing thread orders them before its bulk read with fence.proxy.async.
-constexpr int TMA_GW = 36, TMA_CW = 48;  // landing pitches: floats per value row, bytes per cost row
+constexpr int TMA_GW = 40, TMA_CW = 48;  // landing pitches: floats per value row, bytes per cost row
+constexpr int TMA_GOFF = 4, TMA_COFF = 16;  // columns the boxes start left of the tile
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t) __cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t *bar, int count) {
@@ -1081,20 +1083,20 @@ __global__ void __launch_bounds__(1024 / SW, SW == 4 ? 2 : 1) solver_kernel(Grid
                 if (tid == 0) {
                     fence_proxy_async();
                     mbar_expect_tx(&s_bar, (unsigned) ((TS + 2) * TMA_GW * 4 + (first ? (TS + 1) * TMA_CW : 0)));
-                    tma_load_2d(s_land, &tm.g, &s_bar, GMARGIN + y0 - 1, x0);
-                    if (first) tma_load_2d(s_cland, &tm.c, &s_bar, GMARGIN + y0 + c_r0, x0 + c_r0 + 1);
+                    tma_load_2d(s_land, &tm.g, &s_bar, GMARGIN + y0 - TMA_GOFF, x0);
+                    if (first) tma_load_2d(s_cland, &tm.c, &s_bar, GMARGIN + y0 - TMA_COFF, x0 + c_r0 + 1);
                 }
                 mbar_wait(&s_bar, tma_phase);
                 tma_phase ^= 1u;
                 for (int i = tid; i < (TS + 2) * (TS + 2); i += NT) {
                     const int r = i / (TS + 2), c = i - r * (TS + 2);
-                    sg[r * GP + c] = s_land[r * TMA_GW + c];
+                    sg[r * GP + c] = s_land[r * TMA_GW + c + TMA_GOFF - 1];
                 }
                 if (first) {
                     first = false;
                     for (int i = tid; i < c_rows * c_rows; i += NT) {
                         const int r = i / c_rows, c = i - r * c_rows;
-                        const int b = s_cland[r * TMA_CW + c];
+                        const int b = s_cland[r * TMA_CW + c + TMA_COFF + c_r0];
                         sc[r * CP + c] = (b >= d.thr) ? INF : (float) b;
                     }
                 }

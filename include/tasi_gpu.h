@@ -168,7 +168,7 @@ int tasi_create_sharded(int kind, int level, const int *device_ids, int n_dev, t
 int tasi_nccl_unique_id(void *out128);
 int tasi_create_sharded_rank(int kind, int level, int device, int rank, int n_ranks, const void *nccl_unique_id,
                              tasi_planner **out);
-/* Bands per device (default 4, TASI_BANDS_PER_GPU) and threshold widths of the tile schedule between two exchanges of
+/* Bands per device (default: bands of about 32 tile rows, 2 to 8 per device; TASI_BANDS_PER_GPU) and threshold widths of the tile schedule between two exchanges of
  * the iteration-based mode (default 1, TASI_BAND_PHASES); values < 1 keep the current setting. Before set_map. */
 int tasi_shard_config(tasi_planner *p, int bands_per_device, int phases_per_exchange);
 /* Fused mode on (default) / off (TASI_SHARD_FUSED=0): off keeps the iteration-based exchange (NCCL or peer reads). */

@@ -32,6 +32,7 @@ struct tasi_planner {
     tasi_shard *shard = nullptr;  // set on the handle of a sharded planner (tasi_shard.cuh): every entry point forwards
     int band_rt = 0;              // > 0: this grid is a stack of row bands of band_rt tile rows (a member of a shard)
     int shard_world = 1;          // ... of a grid spread over this many GPUs
+    bool fresh_plan = false;      // the relax launch in flight is an initial plan (tasi_step), not a repair
     const FusedTopo *ft = nullptr;  // fused multi-GPU mode (device pointer; tasi_shard.cuh), nullptr = off
     int *inbox = nullptr;
     int inbox_cap = 0;
@@ -208,6 +209,14 @@ inline int compact_mode(int kind) {
     if (env >= 0 && env <= 2) return env;
     return kind == TASI_FD ? 1 : 0;
 }
+// ... per launch: MFD* gains from the CTA list only where the solve is throughput-bound — the initial plan of a large grid
+// (16384^2: 134.8 -> 130.2 ms; 4096^2 loses, 17.7 -> 19.9 ms, and so does the small active region of a replan)
+inline int compact_for(const tasi_planner *p) {
+    const int c = compact_mode(p->kind);
+    static const bool fixed = getenv("TASI_COMPACT") != nullptr;
+    if (!fixed && p->kind == TASI_MFD && p->fresh_plan && (int64_t) p->TX * p->TY >= 150000 && p->band_rt == 0) return 1;
+    return c;
+}
 // TASI_TMA=1: the relax instances stage their tiles with cp.async.bulk.tensor.2d instead of vector loads (strips only;
 // measured alternative, profiles/r02_tma_staging.txt)
 inline bool tma_mode() {
@@ -226,9 +235,9 @@ solver_fn pick_solver_tma(int kind) {
     }
 }
 // strip = elements per thread of a tile row: 4 (256-thread CTAs, two per SM) or 2 (512-thread CTAs, one per SM)
-solver_fn pick_solver(int kind, int mode, int strip) {
+solver_fn pick_solver(int kind, int mode, int strip, int cmp = -1) {
     if (tma_mode() && mode == 0) return strip == 2 ? pick_solver_tma<2>(kind) : pick_solver_tma<4>(kind);
-    switch (compact_mode(kind)) {
+    switch (cmp >= 0 ? cmp : compact_mode(kind)) {
         case 2: return strip == 2 ? pick_solver_sw<2, 2>(kind, mode) : pick_solver_sw<4, 2>(kind, mode);
         case 1: return strip == 2 ? pick_solver_sw<2, 1>(kind, mode) : pick_solver_sw<4, 1>(kind, mode);
         default: return strip == 2 ? pick_solver_sw<2, 0>(kind, mode) : pick_solver_sw<4, 0>(kind, mode);
@@ -329,6 +338,10 @@ int alloc_grid_dims(tasi_planner *p, int W, int rows, int EX, int EY) {
     int dev_blocks1 = 0;
     CU_TRY(p, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&dev_blocks1, pick_solver(p->kind, 1, strip), nthreads, 0));
     if (dev_blocks1 < dev_blocks) dev_blocks = dev_blocks1;
+    if (p->kind == TASI_MFD) {  // compact_for() may pick the CTA-list instance for an initial plan
+        CU_TRY(p, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&dev_blocks1, pick_solver(p->kind, 0, strip, 1), nthreads, 0));
+        if (dev_blocks1 < dev_blocks) dev_blocks = dev_blocks1;
+    }
     if (dev_blocks < 1) { p->err = "solver kernel does not fit on an SM"; return TASI_ERR_CUDA; }
     int blocks = dev_blocks * p->num_sms;
     if (const char *e = getenv("TASI_BLOCKS_PER_SM")) {
@@ -415,7 +428,7 @@ int run_solver(tasi_planner *p, int mode, float *ms, bool resume = false, float 
     enqueue_seeds_kernel<<<std::min((nt + 255) / 256, 1024), 256, 0, p->stream>>>(d, ordered);
     arm_solver_kernel<<<1, 1, 0, p->stream>>>(d);
     const int nblocks = (p->max_blocks > 0 && p->max_blocks < p->solver_blocks) ? p->max_blocks : p->solver_blocks;
-    pick_solver(p->kind, mode, p->strip)<<<nblocks, TS * TS / p->strip, 0, p->stream>>>(d, p->tm);
+    pick_solver(p->kind, mode, p->strip, compact_for(p))<<<nblocks, TS * TS / p->strip, 0, p->stream>>>(d, p->tm);
     CU_TRY(p, cudaGetLastError());
     CU_TRY(p, cudaEventRecord(p->ev1, p->stream));
     DevCtl h;
@@ -812,7 +825,9 @@ int tasi_step(tasi_planner *p, float *u_ms, float *p_ms, uint64_t *n_updated, ui
     // ReplannerBase.h:64-69 -> plan(); also whenever a focused plan left work parked (the new start may lie beyond
     // what is settled)
     if (fresh || p->num_nodes_updated > 0 || p->pile_open) {
+        p->fresh_plan = fresh;
         rc = run_solver(p, 0, &ms, p->pile_open);
+        p->fresh_plan = false;
         if (rc != TASI_OK) return rc;
         p->stats.kernel_ms_solve = ms;
         p->num_nodes_expanded = p->stats.elem_lowered;

@@ -269,7 +269,7 @@ struct tasi_shard {
     int world = 1;        // ranks of the whole grid
     int my_rank = -1;     // >= 0: one rank per process (multi-process form)
     bool use_nccl = false;
-    int want_per_rank = 4, per_rank = 1, parts = 1;
+    int want_per_rank = 0, per_rank = 1, parts = 1;  // want_per_rank 0 = by grid size (shard_layout)
     int k_phases = 1;
     bool want_fused = true;   // use the fused mode whenever the ranks can map each other's memory
     bool fused = false;       // ... and they do (set by shard_connect_local / tasi_shard_ipc_import)
@@ -352,7 +352,11 @@ int shard_layout(tasi_shard *s, int W, int L) {
     const bool node = sh_node(s);
     const int64_t n_rows = node ? (int64_t) L + 1 : L;
     const int EY = node ? W + 1 : W;
-    int per_rank = std::max(1, s->want_per_rank);
+    // bands per GPU: unless the caller fixed it, bands of about 32 tile rows, between 2 and 8 per GPU (measured, fused mode:
+    // 65536^2 on 8 GPUs 665 ms with 4 bands per GPU, 616 ms with 7-8; 16384^2 on 2 GPUs 130.2 -> 128.4 ms; thinner bands
+    // only add border traffic)
+    int per_rank = s->want_per_rank > 0 ? s->want_per_rank
+                                        : (int) std::min<int64_t>(8, std::max<int64_t>(2, n_rows / ((int64_t) s->world * 32 * TS)));
     int R = 0, parts = 0;
     for (;; --per_rank) {
         parts = s->world * per_rank;
@@ -484,7 +488,7 @@ int shard_fused_run(tasi_shard *s, int mode) {
         enqueue_seeds_kernel<<<std::min((nt + 255) / 256, 1024), 256, 0, p->stream>>>(d, 1);
         const int cap = s->max_blocks > 0 ? s->max_blocks : p->max_blocks;
         const int nblocks = (cap > 0 && cap < p->solver_blocks) ? cap : p->solver_blocks;
-        pick_solver(p->kind, mode, p->strip)<<<nblocks, TS * TS / p->strip, 0, p->stream>>>(d, p->tm);
+        pick_solver(p->kind, mode, p->strip, compact_for(p))<<<nblocks, TS * TS / p->strip, 0, p->stream>>>(d, p->tm);
         SH_TRY(s, cudaGetLastError());
     }
     int rc = shard_sync_all(s);
@@ -724,7 +728,7 @@ int shard_launch_solver(tasi_shard *s, ShardMember &m, int mode) {
     arm_solver_kernel<<<1, 1, 0, p->stream>>>(d);
     const int cap = s->max_blocks > 0 ? s->max_blocks : p->max_blocks;
     const int nblocks = (cap > 0 && cap < p->solver_blocks) ? cap : p->solver_blocks;
-    pick_solver(p->kind, mode, p->strip)<<<nblocks, TS * TS / p->strip, 0, p->stream>>>(d, p->tm);
+    pick_solver(p->kind, mode, p->strip, compact_for(p))<<<nblocks, TS * TS / p->strip, 0, p->stream>>>(d, p->tm);
     SH_TRY(s, cudaGetLastError());
     return TASI_OK;
 }
@@ -1170,8 +1174,8 @@ int shard_init_member(tasi_shard *s, ShardMember &m) {
     SH_TRY(s, cudaEventCreate(&m.ev_t0));
     SH_TRY(s, cudaEventCreate(&m.ev_t1));
     for (cudaEvent_t &e : m.ev_flag) SH_TRY(s, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-    // the limit of the schedule is shared across ranks: every stack keeps the plain band factor (as row bands did)
-    m.p->delta_auto = false;
+    // the band factor follows band_width()'s rule on tiles per GPU / world (every rank holds the same share, so the ranks
+    // agree; the fused mode takes rank 0's width, the iteration mode the widest)
     return TASI_OK;
 }
 

@@ -166,6 +166,8 @@ GridDesc make_desc(const tasi_planner *p) {
     d.inbox = p->inbox;
     d.inbox_cap = p->inbox_cap;
     d.fmode = 0;
+    static const int rel_passes = [] { const char *e = getenv("TASI_REL_PASSES"); return e ? atoi(e) : 8; }();
+    d.rel_passes = rel_passes;
     if (p->focus && !p->open_top && !p->open_bottom && p->band_rt == 0) {
         // Graph::set_start: start_cell_ = Cell(start) rounds (Cell.cpp:20-21); FD*/MFD* wait for the cell's four
         // corner nodes (FieldDPlanner_impl.h:12, Cell.cpp:58-60), MS-DFM for the cell itself

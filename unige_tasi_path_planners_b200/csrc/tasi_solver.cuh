@@ -101,6 +101,7 @@ struct GridDesc {
     int *inbox;            // tiles parked here by OTHER ranks since the last phase boundary (this rank drains it)
     int inbox_cap;
     int fmode;             // fused launch: 0 relax (value-ordered), 1 invalidate (no order: everything parked is released)
+    int rel_passes;        // slices of rising key in which a threshold advance releases the parked tiles (TASI_REL_PASSES)
 };
 
 // TMA staging (solver instances with TMA = 1, TASI_TMA=1): the two CUtensorMap (128 opaque bytes each) the kernel takes
@@ -273,21 +274,31 @@ __device__ inline bool advance_threshold(const GridDesc &d, int *s_red, int tid)
     }
     __syncthreads();
     int *dst = d.far + (cur ^ 1) * d.far_cap;
-    for (int i = tid; i < n; i += nthreads) {
-        const int t = __ldcg(src + i);
-        if (!(*(volatile int *) &d.state[t] & ST_FAR)) continue;  // stale entry (tile was promoted)
-        if (*(volatile int *) &d.key[t] < nthr || nthr == INF_BITS) {
-            if (atomicAnd(&d.state[t], ~ST_FAR) & ST_FAR) {
-                q_push(d, t);
-                atomicAdd(&c->pushes, 1ULL);
+    // The released tiles enter the FIFO queue in REL_PASSES slices of rising key (lowest quarter of the band first), so
+    // that the CTAs start on the tiles whose inputs are final and reach the upper part of the band after its upwind
+    // neighbours have run once (fewer visits on provisional borders). d.rel_passes <= 1: pile order.
+    const float lo = __int_as_float(m), width = (nthr == INF_BITS || m == INF_BITS) ? 0.0f : __int_as_float(nthr) - lo;
+    const int passes = (width > 0.0f && d.rel_passes > 1) ? d.rel_passes : 1;
+    for (int ps = 0; ps < passes; ++ps) {
+        const int cut = (ps == passes - 1) ? nthr : __float_as_int(lo + width * (float) (ps + 1) / (float) passes);
+        for (int i = tid; i < n; i += nthreads) {
+            const int t = __ldcg(src + i);
+            if (!(*(volatile int *) &d.state[t] & ST_FAR)) continue;  // stale entry (tile was promoted), or released by
+                                                                     // an earlier pass
+            const int k = *(volatile int *) &d.key[t];
+            if (k < cut || nthr == INF_BITS) {
+                if (atomicAnd(&d.state[t], ~ST_FAR) & ST_FAR) {
+                    q_push(d, t);
+                    atomicAdd(&c->pushes, 1ULL);
+                }
+            } else if (ps == passes - 1) {
+                const int slot = atomicAdd(&c->far_count[cur ^ 1], 1);
+                if (slot < d.far_cap) dst[slot] = t;
+                else if (atomicAnd(&d.state[t], ~ST_FAR) & ST_FAR) q_push(d, t);
             }
-        } else {
-            const int slot = atomicAdd(&c->far_count[cur ^ 1], 1);
-            if (slot < d.far_cap) dst[slot] = t;
-            else if (atomicAnd(&d.state[t], ~ST_FAR) & ST_FAR) q_push(d, t);
         }
+        __syncthreads();
     }
-    __syncthreads();
     if (tid == 0) c->far_count[cur] = 0;
     return false;
 }
@@ -1220,7 +1231,9 @@ __global__ void __launch_bounds__(1024 / SW, SW == 4 ? 2 : 1) solver_kernel(Grid
             // the CTA's write-back (ordered by the barrier) before the flags below; the leaving thread sits in another
             // warp than the activating ones, so its atomics overlap theirs instead of following them
             if (tid < 8 || tid == LEAVE_TID) {
-                if (fused) fence_sys();
+                // fused mode: only a tile on a band border stores into another GPU's memory and raises its flags; the
+                // values of an interior tile are read by CTAs of this GPU alone, for which the device-scope fence does
+                if (fused && (tx % (d.band_rt + 1) == 0 || tx % (d.band_rt + 1) == d.band_rt - 1)) fence_sys();
                 else fence_gpu();
             }
 

@@ -98,6 +98,19 @@ int tasi_set_map_device(tasi_planner *p, const uint8_t *dev_map, int width, int 
  * n_changed (optional) receives the number of changed cells. */
 int tasi_patch_map(tasi_planner *p, const uint8_t *host_patch, int x, int y, int w, int h, uint64_t *n_changed);
 
+/* tasi_patch_map for callers that must not allocate. NO COUNTERPART IN THE REFERENCE: added
+ * for code under CUDA graph capture, tight serving loops and harnesses that forbid cudaMalloc. Same arguments,
+ * same effect on the cost grid, the same seeds for the next replan and the same n_changed as tasi_patch_map, but the two
+ * scratch buffers of the patch kernels (the device copy of the patch and the per-cell change flags) live in a file-scope
+ * static device array of 2 * TASI_PATCH_STATIC_MAX_CELLS bytes (2 MiB) that every GPU holds from the moment it loads
+ * the library until the process exits; the call makes no cudaMalloc / cudaFree / allocating library call.
+ * A patch of more than TASI_PATCH_STATIC_MAX_CELLS cells (w * h) is rejected with TASI_ERR_ARG and a message naming the
+ * limit (tasi_last_error); a sharded handle with TASI_ERR_STATE. All planners on one GPU share the array and it keeps
+ * the last call's contents (what must start clean is cleared by the call itself): calls that overlap on one GPU — two
+ * planners on their own streams, two host threads — race on it and must be serialised by the caller. */
+#define TASI_PATCH_STATIC_MAX_CELLS (1 << 20)
+int tasi_patch_map_static(tasi_planner *p, const uint8_t *host_patch, int x, int y, int w, int h, uint64_t *n_changed);
+
 /* ReplannerBase::set_start / set_goal (ReplannerBase.h:94-108; Graph.cpp:6-16). Positions are rounded to
  * the element with roundf (Node.cpp:14-17, Cell.cpp:20-21). A goal on a different element forces re-init. */
 int tasi_set_start(tasi_planner *p, float x, float y);

@@ -63,6 +63,7 @@ SIGNATURES = {
     "tasi_set_map": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int]),
     "tasi_set_map_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int64]),
     "tasi_patch_map": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, _u64p]),
+    "tasi_patch_map_static": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, _u64p]),
     "tasi_set_start": (C.c_int, [C.c_void_p, C.c_float, C.c_float]),
     "tasi_set_goal": (C.c_int, [C.c_void_p, C.c_float, C.c_float]),
     "tasi_set_goals": (C.c_int, [C.c_void_p, _f32p, C.c_int]),

@@ -8,6 +8,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <new>
 #include <string>
 #include <vector>
@@ -699,6 +700,78 @@ int tasi_patch_map(tasi_planner *p, const uint8_t *host_patch, int x, int y, int
     CU_TRY(p, cudaGetLastError());
     DevCtl hc;
     int rc = read_ctl(p, &hc);
+    if (rc != TASI_OK) return rc;
+    if (n_changed) *n_changed = hc.n_changed;
+    p->patch_pending = true;
+    return TASI_OK;
+}
+
+// ---- tasi_patch_map_static: the same patch, no allocation ------------------------------------------------------------
+// tasi_patch_map keeps two scratch buffers per planner (the device copy of the patch and the per-cell change flags that
+// patch_apply_kernel hands to patch_seed_kernel) and grows them with cudaFree + cudaMalloc when a larger patch arrives.
+// Callers that must not allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc)
+// get this variant: the scratch is a file-scope array in device memory, 2 x TASI_PATCH_STATIC_MAX_CELLS bytes, that every
+// GPU holds from the moment it loads the library until the process exits. In HOST code `g_patch_scratch` is only a
+// stand-in for the symbol, not a device address: the address the kernels get comes from cudaGetSymbolAddress, taken once
+// per device with that device current (static_patch_scratch below) — no allocation, the array is part of the module image.
+// Every call on a device shares the array; it keeps the last call's contents (both halves are overwritten for the cells
+// of the new patch before they are read: the H2D copy fills the patch half, the flag half is cleared and then written by
+// patch_apply_kernel), and two calls that overlap on one GPU — two planners on their own streams, two host threads —
+// race on it: serialise them.
+static __device__ __align__(256) uint8_t g_patch_scratch[2 * TASI_PATCH_STATIC_MAX_CELLS];
+
+static constexpr int STATIC_SCRATCH_MAX_DEVICES = 64;
+static uint8_t *g_patch_scratch_addr[STATIC_SCRATCH_MAX_DEVICES] = {nullptr};
+static std::mutex g_patch_scratch_mutex;
+
+// device address of g_patch_scratch on the planner's device (which must be current), resolved once per device
+static int static_patch_scratch(tasi_planner *p, uint8_t **out) {
+    if (p->device < 0 || p->device >= STATIC_SCRATCH_MAX_DEVICES) return fail(p, TASI_ERR_ARG, "device index out of range");
+    std::lock_guard<std::mutex> lock(g_patch_scratch_mutex);
+    if (!g_patch_scratch_addr[p->device]) {
+        void *ptr = nullptr;
+        CU_TRY(p, cudaGetSymbolAddress(&ptr, g_patch_scratch));
+        if (!ptr) return fail(p, TASI_ERR_CUDA, "cudaGetSymbolAddress(g_patch_scratch) returned a null address");
+        g_patch_scratch_addr[p->device] = (uint8_t *) ptr;
+    }
+    *out = g_patch_scratch_addr[p->device];
+    return TASI_OK;
+}
+
+int tasi_patch_map_static(tasi_planner *p, const uint8_t *host_patch, int x, int y, int w, int h, uint64_t *n_changed) {
+    if (!p) return TASI_ERR_ARG;
+    if (p->shard) return sh_fail(p->shard, TASI_ERR_STATE, "tasi_patch_map_static: not available on a sharded planner");
+    if (!host_patch || p->initialize_graph) return TASI_ERR_ARG;
+    if (x < 0 || y < 0 || w <= 0 || h <= 0 || (int64_t) x + h > p->rows || (int64_t) y + w > p->W) {
+        p->err = "patch outside the map";  // the reference asserts (Graph.cpp:38-41)
+        return TASI_ERR_ARG;
+    }
+    if ((int64_t) w * h > (int64_t) TASI_PATCH_STATIC_MAX_CELLS) {
+        p->err = "tasi_patch_map_static: patch of " + std::to_string((int64_t) w * h) + " cells exceeds the maximum of " +
+                 std::to_string((int64_t) TASI_PATCH_STATIC_MAX_CELLS) + " cells of the static scratch (use tasi_patch_map)";
+        return TASI_ERR_ARG;
+    }
+    if (p->open_top || p->open_bottom) { p->err = "patch_map is not supported on a band"; return TASI_ERR_STATE; }
+    CU_TRY(p, cudaSetDevice(p->device));
+    uint8_t *scratch = nullptr;
+    int rc = static_patch_scratch(p, &scratch);
+    if (rc != TASI_OK) return rc;
+    uint8_t *patch_buf = scratch, *chg_buf = scratch + TASI_PATCH_STATIC_MAX_CELLS;
+    const size_t n = (size_t) w * h;
+    CU_TRY(p, cudaMemcpyAsync(patch_buf, host_patch, n, cudaMemcpyHostToDevice, p->stream));
+    CU_TRY(p, cudaMemsetAsync(chg_buf, 0, n, p->stream));  // the last call's flags
+    CU_TRY(p, cudaMemsetAsync(&p->ctl->n_changed, 0, sizeof(unsigned long long), p->stream));
+    GridDesc d = make_desc(p);
+    const int blocks = (int) std::min<size_t>((n + 255) / 256, (size_t) p->num_sms * 16);
+    patch_apply_kernel<<<blocks, 256, 0, p->stream>>>(d, patch_buf, chg_buf, x, y, w, h, 0, p->rows);
+    switch (p->kind) {
+        case TASI_FD: patch_seed_kernel<TASI_KIND_FD><<<blocks, 256, 0, p->stream>>>(d, chg_buf, x, y, w, h, 0, p->EX); break;
+        case TASI_DFM: patch_seed_kernel<TASI_KIND_DFM><<<blocks, 256, 0, p->stream>>>(d, chg_buf, x, y, w, h, 0, p->EX); break;
+        default: patch_seed_kernel<TASI_KIND_MFD><<<blocks, 256, 0, p->stream>>>(d, chg_buf, x, y, w, h, 0, p->EX); break;
+    }
+    CU_TRY(p, cudaGetLastError());
+    DevCtl hc;
+    rc = read_ctl(p, &hc);
     if (rc != TASI_OK) return rc;
     if (n_changed) *n_changed = hc.n_changed;
     p->patch_pending = true;

@@ -122,6 +122,20 @@ class GpuPlanner:
         self._check(self._L.tasi_patch_map(self._h, a.ctypes.data_as(C.c_void_p), x, y, ww, hh, C.byref(n)))
         return n.value
 
+    PATCH_STATIC_MAX_CELLS = 1 << 20  # TASI_PATCH_STATIC_MAX_CELLS of include/tasi_gpu.h
+
+    def patch_map_static(self, patch, x, y, w=None, h=None):
+        """patch_map through tasi_patch_map_static: the variant that allocates nothing (scratch in a static device
+        array shared by every planner on the GPU, at most PATCH_STATIC_MAX_CELLS cells per patch; no reference
+        counterpart)."""
+        a = np.ascontiguousarray(patch, dtype=np.uint8)
+        if w is not None and h is not None:
+            a = a.reshape(h, w)
+        hh, ww = a.shape
+        n = C.c_uint64(0)
+        self._check(self._L.tasi_patch_map_static(self._h, a.ctypes.data_as(C.c_void_p), x, y, ww, hh, C.byref(n)))
+        return n.value
+
     def set_start(self, x, y=None):
         if y is None:
             x, y = x

@@ -1,5 +1,6 @@
 """Every instantiation of the tile solver reaches the oracle's field: strips / CTA list / warp lists (TASI_COMPACT),
-2- and 4-element strips (TASI_STRIP), TMA staging (TASI_TMA=1), pile-order release (TASI_REL_PASSES=1). The modes are
+2- and 4-element strips (TASI_STRIP), TMA staging (TASI_TMA=1), pile-order release (TASI_REL_PASSES=1), the FIFO near
+queue (TASI_BUCKETS=0) and other ring counts of the bucketed one. The modes are
 read once per process, so each runs in a worker process (tests/_mode_worker.py)."""
 import os
 import subprocess
@@ -11,10 +12,11 @@ import pytest
 from unige_tasi_path_planners_b200 import synth
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-KNOBS = ("TASI_TMA", "TASI_COMPACT", "TASI_STRIP", "TASI_REL_PASSES", "TASI_DELTA_FACTOR")
+KNOBS = ("TASI_TMA", "TASI_COMPACT", "TASI_STRIP", "TASI_REL_PASSES", "TASI_DELTA_FACTOR", "TASI_BUCKETS")
 MODES = [{"TASI_TMA": "1"}, {"TASI_TMA": "1", "TASI_STRIP": "2"}, {"TASI_COMPACT": "0"}, {"TASI_COMPACT": "1"},
          {"TASI_COMPACT": "2"}, {"TASI_COMPACT": "1", "TASI_STRIP": "4"}, {"TASI_STRIP": "4"}, {"TASI_REL_PASSES": "1"},
-         {"TASI_REL_PASSES": "32", "TASI_DELTA_FACTOR": "6"}]
+         {"TASI_REL_PASSES": "32", "TASI_DELTA_FACTOR": "6"}, {"TASI_BUCKETS": "0"}, {"TASI_BUCKETS": "4"},
+         {"TASI_BUCKETS": "16", "TASI_DELTA_FACTOR": "3"}]
 
 
 @pytest.fixture(scope="module")

@@ -68,6 +68,9 @@ struct tasi_planner {
     uint8_t *seed = nullptr;
     int *key = nullptr, *far = nullptr;
     int far_cap = 0;
+    int *bq = nullptr;   // rings of the bucketed near queue (TASI_BUCKETS), nb x bqsize slots
+    int nb = 30;
+    unsigned bqsize = 0;
     unsigned long long *cost_sum = nullptr;  // device: {sum of free-cell costs, number of free cells}
     bool cost_stats_valid = false;
     float mean_cost = 1.0f;
@@ -134,6 +137,13 @@ inline float band_width(const tasi_planner *p) {
         double nt = std::max(1.0, (double) p->TX * (double) p->TY);
         if (shard_rule && p->shard_world > 1) nt = std::max(1.0, nt / (double) p->shard_world);
         f = (float) std::min(6.0, std::max(2.0, 2.0 + 0.5 * std::log2(262144.0 / nt)));
+        // bucketed near queue: the order inside the band comes from the rings, so the band can be wide and the phase
+        // barriers few (measured, 30 rings: best factor 32 up to 4096^2, 24 at 8192^2, 8-16 at 16384^2, 8-12 beyond)
+        // (initial plans; a repair works on a small active region: factor 4 balances the three patch kinds of cfg3,
+        // profiles/r02_cfg3_repair_factor.txt)
+        if (p->bq && p->fresh_plan) f = (float) std::min(32.0, std::max(8.0, 12.0 + 5.0 * std::log2(262144.0 / nt)));
+        static const float repair_f = [] { const char *e = getenv("TASI_REPAIR_FACTOR"); return e ? (float) atof(e) : 0.0f; }();
+        if (p->bq && !p->fresh_plan) f = repair_f > 0.0f ? repair_f : std::max(f, 4.0f);  // cfg3 sweep: 3 / 4 / 6 / 8 / 12
     }
     return f * (float) TS * p->mean_cost;
 }
@@ -169,6 +179,11 @@ GridDesc make_desc(const tasi_planner *p) {
     d.fmode = 0;
     static const int rel_passes = [] { const char *e = getenv("TASI_REL_PASSES"); return e ? atoi(e) : 8; }();
     d.rel_passes = rel_passes;
+    // bucketed near queue: relax launches of an unsharded grid (run_solver switches it off for the invalidate launch)
+    d.nb = (p->bq && p->band_rt == 0 && !p->open_top && !p->open_bottom && !p->ft && p->delta_factor > 0.0f) ? p->nb : 0;
+    d.bq = p->bq;
+    d.bqmask = p->bqsize ? p->bqsize - 1 : 0;
+    d.inv_bw = d.nb > 0 && d.delta > 0.0f ? (float) d.nb / d.delta : 0.0f;
     if (p->focus && !p->open_top && !p->open_bottom && p->band_rt == 0) {
         // Graph::set_start: start_cell_ = Cell(start) rounds (Cell.cpp:20-21); FD*/MFD* wait for the cell's four
         // corner nodes (FieldDPlanner_impl.h:12, Cell.cpp:58-60), MS-DFM for the cell itself
@@ -184,7 +199,8 @@ GridDesc make_desc(const tasi_planner *p) {
 
 void free_grid(tasi_planner *p) {
     cudaFree(p->g_base); cudaFree(p->c_base); cudaFree(p->state); cudaFree(p->queue); cudaFree(p->seed);
-    cudaFree(p->stage); cudaFree(p->key); cudaFree(p->far);
+    cudaFree(p->stage); cudaFree(p->key); cudaFree(p->far); cudaFree(p->bq);
+    p->bq = nullptr;
     p->key = nullptr; p->far = nullptr;
     p->g_base = nullptr; p->c_base = nullptr; p->state = nullptr; p->queue = nullptr; p->seed = nullptr;
     p->stage = nullptr;
@@ -301,6 +317,14 @@ int alloc_grid_arrays(tasi_planner *p, int EY, int nt, unsigned q) {
     CU_TRY(p, cudaMemsetAsync(p->state, 0, sizeof(int) * nt, p->stream));
     CU_TRY(p, cudaMemsetAsync(p->queue, 0, sizeof(int) * q, p->stream));
     CU_TRY(p, cudaMemsetAsync(p->seed, 0, nt, p->stream));
+    p->bqsize = 0;
+    if (p->nb > 0 && p->band_rt == 0 && !p->open_top && !p->open_bottom) {
+        unsigned bs = 1;
+        while (bs < (unsigned) nt + 1u) bs <<= 1;
+        CU_TRY(p, cudaMalloc(&p->bq, sizeof(int) * (size_t) bs * p->nb));
+        CU_TRY(p, cudaMemsetAsync(p->bq, 0, sizeof(int) * (size_t) bs * p->nb, p->stream));
+        p->bqsize = bs;
+    }
     if (tma_mode()) return make_tensor_maps(p);
     return TASI_OK;
 }
@@ -409,7 +433,9 @@ int run_solver(tasi_planner *p, int mode, float *ms, bool resume = false, float 
     int rcs = ensure_cost_stats(p);
     if (rcs != TASI_OK) return rcs;
     GridDesc d = make_desc(p);
-    if (mode == 1) d.n_focus = 0;
+    if (mode == 1) { d.n_focus = 0; d.nb = 0; }
+    static const bool repair_buckets = [] { const char *e = getenv("TASI_REPAIR_BUCKETS"); return !e || atoi(e) != 0; }();
+    if (!p->fresh_plan && !repair_buckets) d.nb = 0;
     DevCtl z;
     memset(&z, 0, sizeof z);
     z.timeout_ns = (unsigned long long) (p->timeout_s * 1e9);
@@ -472,6 +498,7 @@ int run_solver(tasi_planner *p, int mode, float *ms, bool resume = false, float 
         // leave the queue/state arrays clean for the next attempt
         cudaMemsetAsync(p->state, 0, sizeof(int) * nt, p->stream);
         cudaMemsetAsync(p->queue, 0, sizeof(int) * p->qsize, p->stream);
+        if (p->bq) cudaMemsetAsync(p->bq, 0, sizeof(int) * (size_t) p->bqsize * p->nb, p->stream);
         p->initialize_search = true;
         return TASI_ERR_TIMEOUT;
     }
@@ -527,6 +554,10 @@ int tasi_create(int kind, int level, int device, tasi_planner **out) {
     if (const char *e = getenv("TASI_TIMEOUT_S")) {
         double v = atof(e);
         if (v > 0) p->timeout_s = v;
+    }
+    if (const char *e = getenv("TASI_BUCKETS")) {  // key-ordered rings of the near queue (0 = one FIFO ring)
+        const int v = atoi(e);
+        if (v >= 0 && v <= 30) p->nb = v;
     }
     if (const char *e = getenv("TASI_DELTA_FACTOR")) {  // fixed factor; <= 0: no ordering
         p->delta_factor = (float) atof(e);

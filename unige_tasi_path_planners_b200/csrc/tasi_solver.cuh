@@ -40,6 +40,8 @@ constexpr int ST_SHIFT = 8;    // bits (which halo sides changed since the tile 
 constexpr int INF_BITS = 0x7f800000;
 constexpr int GMARGIN = 32;    // columns of margin left of element/cell column 0 (keeps rows 128B aligned)
 
+constexpr int QB_MAX = 32;     // size of the ring counter arrays of the bucketed near queue (at most 30 rings: one lane each)
+
 struct DevCtl {
     unsigned long long head, tail;  // ticket counters of the work queue
     int pending;                    // tiles queued or running
@@ -61,6 +63,10 @@ struct DevCtl {
     int focus_hit;                  // the launch ended because the focus elements were settled (work stays parked)
     int launches;                   // solver launches since the counters were last cleared (sharded loop)
     unsigned long long busy_ns;     // globaltimer span of the solver launches as CTA 0 saw them, summed
+    // bucketed near queue (GridDesc::nb > 0): ticket counters of the key-ordered rings, one 128-byte line each
+    alignas(128) unsigned long long bhead[QB_MAX];
+    alignas(128) unsigned long long btail[QB_MAX];
+    alignas(128) int bcount[QB_MAX];  // published entries of each ring not yet claimed by a popper
     // patch bookkeeping
     unsigned long long n_changed, n_raised, n_lowered_cells, n_seed_elems;
     unsigned long long halo_lowered;
@@ -102,6 +108,15 @@ struct GridDesc {
     int inbox_cap;
     int fmode;             // fused launch: 0 relax (value-ordered), 1 invalidate (no order: everything parked is released)
     int rel_passes;        // slices of rising key in which a threshold advance releases the parked tiles (TASI_REL_PASSES)
+    // bucketed near queue (TASI_BUCKETS = nb > 0, relax launches of an unsharded grid): tiles that are due now go to one
+    // of nb rings by key — ring b holds the keys of slice b of the current value band [threshold - delta, threshold) —
+    // and a CTA looking for work takes from the lowest non-empty ring (after the plain ring `queue`, which keeps the
+    // entries without an order: overflow fall-backs). No barrier between the rings: an ordered-by-integer-metric
+    // worklist inside each threshold phase.
+    int nb;
+    int *bq;               // nb rings of bqmask + 1 slots (a power of two > tiles: a tile is queued at most once)
+    unsigned bqmask;
+    float inv_bw;          // nb / delta
 };
 
 // TMA staging (solver instances with TMA = 1, TASI_TMA=1): the two CUtensorMap (128 opaque bytes each) the kernel takes
@@ -134,7 +149,40 @@ __device__ __forceinline__ void q_fail(const GridDesc &d) {
     atomicExch(&d.ctl->done, 1);
 }
 
+__device__ __forceinline__ int cur_thr_bits(const GridDesc &d);
+
+// ring of the bucketed near queue for key `kbits` (-1 = the plain ring)
+__device__ __forceinline__ int bucket_of(const GridDesc &d, int kbits) {
+    if (d.nb <= 0) return -1;
+    const int tb = cur_thr_bits(d);
+    if (tb == INF_BITS || kbits == INF_BITS) return 0;
+    const float x = (__int_as_float(kbits) - (__int_as_float(tb) - d.delta)) * d.inv_bw;
+    const int b = x > 0.0f ? (int) x : 0;
+    return b < d.nb ? b : d.nb - 1;
+}
+
+// push with a key: into the ring of its slice of the band (bucketed near queue), else the plain ring
+__device__ inline void q_push_key(const GridDesc &d, int tile, int kbits) {
+    const int b = bucket_of(d, kbits);
+    if (b < 0) {
+        atomicAdd(&d.ctl->pending, 1);
+        unsigned long long t = atomicAdd(&d.ctl->tail, 1ULL);
+        atomicExch(&d.queue[(unsigned) t & d.qmask], tile + 1);
+        return;
+    }
+    atomicAdd(&d.ctl->pending, 1);
+    unsigned long long t = atomicAdd(&d.ctl->btail[b], 1ULL);
+    atomicExch(&d.bq[(size_t) b * (d.bqmask + 1u) + ((unsigned) t & d.bqmask)], tile + 1);
+    __threadfence();
+    atomicAdd(&d.ctl->bcount[b], 1);  // after the slot: a popper that wins a unit of the count finds its slot filled
+                                      // (or about to be, by a pusher that already holds its ticket)
+}
+
 __device__ inline void q_push(const GridDesc &d, int tile) {
+    if (d.nb > 0) {  // bucketed near queue: by the tile's current key
+        q_push_key(d, tile, *(volatile int *) &d.key[tile]);
+        return;
+    }
     atomicAdd(&d.ctl->pending, 1);
     unsigned long long t = atomicAdd(&d.ctl->tail, 1ULL);
     // The ring has 2 x max(tiles, CTAs) + 1 slots and a tile is queued at most once, so the slot of this ticket was
@@ -176,6 +224,67 @@ __device__ inline int q_pop(const GridDesc &d) {
     }
 }
 
+// q_pop of the bucketed near queue, called by the 32 lanes of warp 0 together: lane b looks at the count of ring b (one
+// coalesced read per poll), the lowest ring with entries is tried: a unit of its count is taken with an unconditional
+// atomic (given back if the count was already spent — no CAS loop, so hundreds of CTAs do not serialise on one word),
+// then a ticket of its head, whose slot is filled or about to be. Nobody commits to a ring that may never be fed again.
+// Lane 31 watches the plain ring (entries queued without an order before the launch). Returns the same value to every lane.
+__device__ inline int q_pop_warp(const GridDesc &d, int lane) {
+    DevCtl *c = d.ctl;
+    const unsigned full = 0xffffffffu;
+    const int b = lane & (QB_MAX - 1);
+    int *ring = d.bq + (size_t) b * (d.bqmask + 1u);
+    const bool mine = lane < d.nb;
+    unsigned long long t0 = 0, sum0 = 0;
+    unsigned ns = 32, polls = 0;
+    for (;;) {
+        int cnt = 0;
+        unsigned long long ph = 0, pt = 0;
+        if (mine) cnt = *(volatile int *) &c->bcount[b];
+        if (lane == 31) {
+            ph = *(volatile unsigned long long *) &c->head;
+            pt = *(volatile unsigned long long *) &c->tail;
+        }
+        const unsigned m = __ballot_sync(full, (mine && cnt > 0) || (lane == 31 && ph < pt));
+        if (m) {
+            const int src = __ffs(m) - 1;
+            int v = 0;
+            if (lane == src) {
+                volatile int *slot = nullptr;
+                if (lane == 31) {
+                    if (atomicCAS(&c->head, ph, ph + 1ULL) == ph) slot = &d.queue[(unsigned) ph & d.qmask];
+                } else if (atomicSub(&c->bcount[b], 1) > 0) {
+                    const unsigned long long h = atomicAdd(&c->bhead[b], 1ULL);
+                    slot = &ring[(unsigned) h & d.bqmask];
+                } else {
+                    atomicAdd(&c->bcount[b], 1);  // spent meanwhile: give the unit back
+                }
+                if (slot) {
+                    while ((v = *slot) == 0) {}
+                    *slot = 0;
+                }
+            }
+            v = __shfl_sync(full, v, src);
+            if (v) return v - 1;
+            continue;  // somebody else took it: look again
+        }
+        int stop = 0;
+        if (lane == 0) {
+            if (*(volatile int *) &c->done) stop = 1;
+            else if ((++polls & 63u) == 0) {
+                // watchdog on GLOBAL progress: nothing pushed anywhere for timeout_ns
+                unsigned long long sum = *(volatile unsigned long long *) &c->tail;
+                for (int i = 0; i < d.nb; ++i) sum += *(volatile unsigned long long *) &c->btail[i];
+                if (t0 == 0 || sum != sum0) { t0 = globaltimer_ns(); sum0 = sum; }
+                else if (globaltimer_ns() - t0 > c->timeout_ns) { q_fail(d); stop = 1; }
+            }
+        }
+        if (__shfl_sync(full, stop, 0)) return -1;
+        __nanosleep(ns);
+        if (ns < Q_SLEEP_MAX_NS) ns <<= 1;
+    }
+}
+
 // ---- near / far scheduling -------------------------------------------------------------------------------------
 // Every activation carries a key: the lowest changed value the tile is about to read. Tiles keyed below the
 // current threshold go to the work queue ("near"); the others are parked in the far pile until the queue has
@@ -206,7 +315,7 @@ __device__ inline void activate(const GridDesc &d, int tile, int kbits, int dirb
     const int st = old & ST_MASK;
     if (st == 0) {  // it was idle: ours to queue
         if (near) {
-            q_push(d, tile);
+            q_push_key(d, tile, kbits);
             atomicAdd(&d.ctl->pushes, 1ULL);
         } else {
             atomicOr(&d.state[tile], ST_FAR);
@@ -215,7 +324,7 @@ __device__ inline void activate(const GridDesc &d, int tile, int kbits, int dirb
     } else if ((st & ST_FAR) && near) {
         // parked with a higher key: promote (whoever clears ST_FAR owns the push; the pile entry goes stale)
         if (atomicAnd(&d.state[tile], ~ST_FAR) & ST_FAR) {
-            q_push(d, tile);
+            q_push_key(d, tile, kbits);
             atomicAdd(&d.ctl->pushes, 1ULL);
         }
     }
@@ -288,7 +397,7 @@ __device__ inline bool advance_threshold(const GridDesc &d, int *s_red, int tid)
             const int k = *(volatile int *) &d.key[t];
             if (k < cut || nthr == INF_BITS) {
                 if (atomicAnd(&d.state[t], ~ST_FAR) & ST_FAR) {
-                    q_push(d, t);
+                    q_push_key(d, t, k);
                     atomicAdd(&c->pushes, 1ULL);
                 }
             } else if (ps == passes - 1) {
@@ -1045,7 +1154,18 @@ __global__ void __launch_bounds__(1024 / SW, SW == 4 ? 2 : 1) solver_kernel(Grid
     }
 
     for (;;) {
-        if (tid == 0) {
+        if (d.nb > 0 && tid < 32) {  // bucketed near queue: warp 0 pops together (never in fused mode)
+            const int t = q_pop_warp(d, tid);
+            if (tid == 0) {
+                if (t >= 0) {
+                    const int old = atomicExch(&d.state[t], ST_RUN);
+                    s_inmask = old >> ST_SHIFT;
+                    atomicExch(&d.key[t], INF_BITS);
+                    fence_gpu();
+                }
+                s_tile = t;
+            }
+        } else if (d.nb <= 0 && tid == 0) {
             int t = (fused && blockIdx.x == 0) ? q_pop_fused(d, &ticket) : q_pop(d);
             if (t >= 0) {
                 // claim the tile: the word we take away carries the direction bits of every activation so far;

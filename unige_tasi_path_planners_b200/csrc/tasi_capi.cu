@@ -233,7 +233,7 @@ inline int compact_mode(int kind) {
 inline int compact_for(const tasi_planner *p) {
     const int c = compact_mode(p->kind);
     static const bool fixed = getenv("TASI_COMPACT") != nullptr;
-    if (!fixed && p->kind == TASI_MFD && p->fresh_plan && (int64_t) p->TX * p->TY >= 150000 && p->band_rt == 0) return 1;
+    if (!fixed && p->kind == TASI_MFD && p->fresh_plan && (int64_t) p->TX * p->TY >= 50000 && p->band_rt == 0) return 1;
     return c;
 }
 // TASI_TMA=1: the relax instances stage their tiles with cp.async.bulk.tensor.2d instead of vector loads (strips only;
@@ -354,7 +354,9 @@ int alloc_grid_dims(tasi_planner *p, int W, int rows, int EX, int EY) {
     // extra tile in flight wins. Measured cross-over (tiles), per operator weight (scripts/quick_bench.py with
     // TASI_STRIP=2|4; FD* 4096^2 34.1 -> 30.0 ms, 8192^2 97 -> 86 ms; MFD* 4096^2 21.5 -> 18.0 ms; MS-DFM 2048^2 8.4 -> 8.1;
     // re-measured after the in-strip Gauss-Seidel order: MFD* 8192^2 is 52.9 ms with 2-element strips, 46.4 ms with 4):
-    const int strip2_upto = p->kind == TASI_FD ? 100000 : (p->kind == TASI_MFD ? 33000 : 4200);
+    // (re-measured under the bucketed near queue, profiles/r02_buckets_strip_x_compaction.txt: FD* 8192^2 = 66 k tiles is
+    // 55.6 ms with 2-element strips, 48.4 ms with 4)
+    const int strip2_upto = p->kind == TASI_DFM ? 4200 : 33000;
     int strip = nt <= strip2_upto ? 2 : 4;
     if (const char *e = getenv("TASI_STRIP")) {
         const int v = atoi(e);

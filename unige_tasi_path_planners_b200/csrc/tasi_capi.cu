@@ -127,6 +127,14 @@ inline bool node_based(const tasi_planner *p) { return p->kind != TASI_DFM; }
 // 8192^2 / 4096^2, 6-8 at 2048^2 / 1024^2, within a 15 % spread — small grids have too short a front to feed the
 // CTAs otherwise. Row bands keep the plain factor (their threshold is shared across ranks), and so do focused plans
 // (the band is the granularity at which they can stop).
+// rings of the bucketed near queue a relax launch of this planner uses (0 = the FIFO ring): unsharded grids and the fused
+// launches of a sharded grid; the iteration-based exchange and row bands keep the FIFO ring
+inline int active_rings(const tasi_planner *p) {
+    static const bool fused_buckets = [] { const char *e = getenv("TASI_FUSED_BUCKETS"); return !e || atoi(e) != 0; }();
+    return (p->bq && !p->open_top && !p->open_bottom && p->delta_factor > 0.0f &&
+            (p->band_rt == 0 || (p->ft && fused_buckets))) ? p->nb : 0;
+}
+
 inline float band_width(const tasi_planner *p) {
     float f = p->delta_factor;
     if (p->delta_auto && f > 0.0f && !p->focus && !p->open_top && !p->open_bottom) {
@@ -141,9 +149,9 @@ inline float band_width(const tasi_planner *p) {
         // barriers few (measured, 30 rings: best factor 32 up to 4096^2, 24 at 8192^2, 8-16 at 16384^2, 8-12 beyond)
         // (initial plans; a repair works on a small active region: factor 4 balances the three patch kinds of cfg3,
         // profiles/r02_cfg3_repair_factor.txt)
-        if (p->bq && p->fresh_plan) f = (float) std::min(32.0, std::max(8.0, 12.0 + 5.0 * std::log2(262144.0 / nt)));
+        if (active_rings(p) > 0 && (p->fresh_plan || p->band_rt > 0)) f = (float) std::min(32.0, std::max(8.0, 12.0 + 5.0 * std::log2(262144.0 / nt)));
         static const float repair_f = [] { const char *e = getenv("TASI_REPAIR_FACTOR"); return e ? (float) atof(e) : 0.0f; }();
-        if (p->bq && !p->fresh_plan) f = repair_f > 0.0f ? repair_f : std::max(f, 4.0f);  // cfg3 sweep: 3 / 4 / 6 / 8 / 12
+        if (active_rings(p) > 0 && !p->fresh_plan && p->band_rt == 0) f = repair_f > 0.0f ? repair_f : std::max(f, 4.0f);  // cfg3 sweep: 3 / 4 / 6 / 8 / 12
     }
     return f * (float) TS * p->mean_cost;
 }
@@ -180,7 +188,7 @@ GridDesc make_desc(const tasi_planner *p) {
     static const int rel_passes = [] { const char *e = getenv("TASI_REL_PASSES"); return e ? atoi(e) : 8; }();
     d.rel_passes = rel_passes;
     // bucketed near queue: relax launches of an unsharded grid (run_solver switches it off for the invalidate launch)
-    d.nb = (p->bq && p->band_rt == 0 && !p->open_top && !p->open_bottom && !p->ft && p->delta_factor > 0.0f) ? p->nb : 0;
+    d.nb = active_rings(p);
     d.bq = p->bq;
     d.bqmask = p->bqsize ? p->bqsize - 1 : 0;
     d.inv_bw = d.nb > 0 && d.delta > 0.0f ? (float) d.nb / d.delta : 0.0f;
@@ -318,7 +326,7 @@ int alloc_grid_arrays(tasi_planner *p, int EY, int nt, unsigned q) {
     CU_TRY(p, cudaMemsetAsync(p->queue, 0, sizeof(int) * q, p->stream));
     CU_TRY(p, cudaMemsetAsync(p->seed, 0, nt, p->stream));
     p->bqsize = 0;
-    if (p->nb > 0 && p->band_rt == 0 && !p->open_top && !p->open_bottom) {
+    if (p->nb > 0 && !p->open_top && !p->open_bottom) {
         unsigned bs = 1;
         while (bs < (unsigned) nt + 1u) bs <<= 1;
         CU_TRY(p, cudaMalloc(&p->bq, sizeof(int) * (size_t) bs * p->nb));
@@ -1452,9 +1460,9 @@ int tasi_shard_set_fused(tasi_planner *p, int enabled) {
 
 namespace {
 struct ShardIpcBlob {
-    cudaIpcMemHandle_t g, state, key, queue, ctl, fc, inbox;
+    cudaIpcMemHandle_t g, state, key, queue, ctl, fc, inbox, bq;
     int64_t gpitch;
-    int qmask, far_cap, TY, inbox_cap, rank, valid;
+    int qmask, far_cap, TY, inbox_cap, rank, valid, bqmask, has_bq;
 };
 }  // namespace
 
@@ -1476,6 +1484,11 @@ int tasi_shard_ipc_export(tasi_planner *p, void *blob) {
     SH_TRY(s, cudaIpcGetMemHandle(&b.ctl, q->ctl));
     SH_TRY(s, cudaIpcGetMemHandle(&b.fc, m.fc));
     SH_TRY(s, cudaIpcGetMemHandle(&b.inbox, q->inbox));
+    if (q->bq) {
+        SH_TRY(s, cudaIpcGetMemHandle(&b.bq, q->bq));
+        b.has_bq = 1;
+        b.bqmask = (int) (q->bqsize - 1);
+    }
     b.gpitch = q->gpitch; b.qmask = (int) (q->qsize - 1); b.far_cap = q->far_cap; b.TY = q->TY;
     b.inbox_cap = q->inbox_cap; b.rank = m.rank; b.valid = 1;
     memset(blob, 0, tasi_shard_ipc_size());
@@ -1533,6 +1546,12 @@ int tasi_shard_ipc_import(tasi_planner *p, const void *blobs_by_rank) {
         d.far = nullptr; d.far_cap = b.far_cap;
         d.ctl = (DevCtl *) ct;
         d.inbox = (int *) ib; d.inbox_cap = b.inbox_cap;
+        d.bq = nullptr; d.bqmask = 0;
+        if (b.has_bq) {
+            void *bqp = nullptr;
+            if ((rc = open(b.bq, &bqp)) != TASI_OK) return rc;
+            d.bq = (int *) bqp; d.bqmask = (unsigned) b.bqmask;
+        }
         d.TY = b.TY;
         d.seed = nullptr; d.xgoals = nullptr;
         nb[k] = d;

@@ -205,6 +205,7 @@ __global__ void fused_rearm_kernel(GridDesc d, FusedCtl *fc, FusedTopo *topo, in
     c->thr_bits = mode == 1 ? INF_BITS : 0;
     c->far_sel = 0;
     c->far_count[0] = c->far_count[1] = 0;
+    for (int b = 0; b < QB_MAX; ++b) { c->bhead[b] = c->btail[b] = 0; c->bcount[b] = 0; }
     fc->inbox_count = 0;
     fc->rx = fc->tx = 0;
     if (rank == 0) fc->active = 0;
@@ -482,6 +483,7 @@ int shard_fused_run(tasi_shard *s, int mode) {
         GridDesc d = make_desc(p);
         d.n_focus = 0;
         d.fmode = mode;
+        if (mode == 1) d.nb = 0;  // the invalidate launch has no order
         const int nt = p->TX * p->TY;
         fused_rearm_kernel<<<1, 1, 0, p->stream>>>(d, m.fc, m.topo, mode, m.rank);
         if (mode == 0) seed_keys_kernel<<<std::min((nt + 7) / 8, p->num_sms * 8), 256, 0, p->stream>>>(d);

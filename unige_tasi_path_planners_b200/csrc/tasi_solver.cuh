@@ -224,67 +224,6 @@ __device__ inline int q_pop(const GridDesc &d) {
     }
 }
 
-// q_pop of the bucketed near queue, called by the 32 lanes of warp 0 together: lane b looks at the count of ring b (one
-// coalesced read per poll), the lowest ring with entries is tried: a unit of its count is taken with an unconditional
-// atomic (given back if the count was already spent — no CAS loop, so hundreds of CTAs do not serialise on one word),
-// then a ticket of its head, whose slot is filled or about to be. Nobody commits to a ring that may never be fed again.
-// Lane 31 watches the plain ring (entries queued without an order before the launch). Returns the same value to every lane.
-__device__ inline int q_pop_warp(const GridDesc &d, int lane) {
-    DevCtl *c = d.ctl;
-    const unsigned full = 0xffffffffu;
-    const int b = lane & (QB_MAX - 1);
-    int *ring = d.bq + (size_t) b * (d.bqmask + 1u);
-    const bool mine = lane < d.nb;
-    unsigned long long t0 = 0, sum0 = 0;
-    unsigned ns = 32, polls = 0;
-    for (;;) {
-        int cnt = 0;
-        unsigned long long ph = 0, pt = 0;
-        if (mine) cnt = *(volatile int *) &c->bcount[b];
-        if (lane == 31) {
-            ph = *(volatile unsigned long long *) &c->head;
-            pt = *(volatile unsigned long long *) &c->tail;
-        }
-        const unsigned m = __ballot_sync(full, (mine && cnt > 0) || (lane == 31 && ph < pt));
-        if (m) {
-            const int src = __ffs(m) - 1;
-            int v = 0;
-            if (lane == src) {
-                volatile int *slot = nullptr;
-                if (lane == 31) {
-                    if (atomicCAS(&c->head, ph, ph + 1ULL) == ph) slot = &d.queue[(unsigned) ph & d.qmask];
-                } else if (atomicSub(&c->bcount[b], 1) > 0) {
-                    const unsigned long long h = atomicAdd(&c->bhead[b], 1ULL);
-                    slot = &ring[(unsigned) h & d.bqmask];
-                } else {
-                    atomicAdd(&c->bcount[b], 1);  // spent meanwhile: give the unit back
-                }
-                if (slot) {
-                    while ((v = *slot) == 0) {}
-                    *slot = 0;
-                }
-            }
-            v = __shfl_sync(full, v, src);
-            if (v) return v - 1;
-            continue;  // somebody else took it: look again
-        }
-        int stop = 0;
-        if (lane == 0) {
-            if (*(volatile int *) &c->done) stop = 1;
-            else if ((++polls & 63u) == 0) {
-                // watchdog on GLOBAL progress: nothing pushed anywhere for timeout_ns
-                unsigned long long sum = *(volatile unsigned long long *) &c->tail;
-                for (int i = 0; i < d.nb; ++i) sum += *(volatile unsigned long long *) &c->btail[i];
-                if (t0 == 0 || sum != sum0) { t0 = globaltimer_ns(); sum0 = sum; }
-                else if (globaltimer_ns() - t0 > c->timeout_ns) { q_fail(d); stop = 1; }
-            }
-        }
-        if (__shfl_sync(full, stop, 0)) return -1;
-        __nanosleep(ns);
-        if (ns < Q_SLEEP_MAX_NS) ns <<= 1;
-    }
-}
-
 // ---- near / far scheduling -------------------------------------------------------------------------------------
 // Every activation carries a key: the lowest changed value the tile is about to read. Tiles keyed below the
 // current threshold go to the work queue ("near"); the others are parked in the far pile until the queue has
@@ -499,8 +438,16 @@ __device__ inline void activate_remote(const GridDesc &d, const GridDesc &r, Fus
     if (push) {
         fused_rank_wakes(d);  // BEFORE the count of the other rank can leave 0 ...
         if (atomicAdd_system(&r.ctl->pending, 1) != 0) fused_rank_idles(d);  // ... it was awake already
-        const unsigned long long t = atomicAdd_system(&r.ctl->tail, 1ULL);
-        atomicExch_system(&r.queue[(unsigned) t & r.qmask], tile + 1);
+        if (d.nb > 0 && r.bq) {  // bucketed near queue (every rank runs the same configuration): the ring of the key
+            const int b = bucket_of(d, kbits);
+            const unsigned long long t = atomicAdd_system(&r.ctl->btail[b], 1ULL);
+            atomicExch_system(&r.bq[(size_t) b * (r.bqmask + 1u) + ((unsigned) t & r.bqmask)], tile + 1);
+            fence_sys();
+            atomicAdd_system(&r.ctl->bcount[b], 1);
+        } else {
+            const unsigned long long t = atomicAdd_system(&r.ctl->tail, 1ULL);
+            atomicExch_system(&r.queue[(unsigned) t & r.qmask], tile + 1);
+        }
         atomicAdd_system(&rfc->rx, 1ULL);
     }
     atomicAdd(&d.ft->fc[d.ft->rank]->tx, 1ULL);
@@ -699,6 +646,72 @@ __device__ inline int q_pop_fused(const GridDesc &d, unsigned long long *ticket)
             tail0 = tl;
             t0 = globaltimer_ns();
         }
+        __nanosleep(ns);
+        if (ns < Q_SLEEP_MAX_NS) ns <<= 1;
+    }
+}
+
+// q_pop of the bucketed near queue, called by the 32 lanes of warp 0 together: lane b looks at the count of ring b (one
+// coalesced read per poll), the lowest ring with entries is tried: a unit of its count is taken with an unconditional
+// atomic (given back if the count was already spent — no CAS loop, so hundreds of CTAs do not serialise on one word),
+// then a ticket of its head, whose slot is filled or about to be. Nobody commits to a ring that may never be fed again.
+// Lane 31 watches the plain ring (entries queued without an order before the launch). Returns the same value to every lane.
+// fused0: CTA 0 of a fused multi-GPU launch, which also serves the coordinator (returns -2: call fused_service).
+__device__ inline int q_pop_warp(const GridDesc &d, int lane, bool fused0) {
+    DevCtl *c = d.ctl;
+    const unsigned full = 0xffffffffu;
+    const int b = lane & (QB_MAX - 1);
+    int *ring = d.bq + (size_t) b * (d.bqmask + 1u);
+    const bool mine = lane < d.nb;
+    unsigned long long t0 = 0, sum0 = 0;
+    unsigned ns = 32, polls = 0;
+    for (;;) {
+        int cnt = 0;
+        unsigned long long ph = 0, pt = 0;
+        if (mine) cnt = *(volatile int *) &c->bcount[b];
+        if (lane == 31) {
+            ph = *(volatile unsigned long long *) &c->head;
+            pt = *(volatile unsigned long long *) &c->tail;
+        }
+        const unsigned m = __ballot_sync(full, (mine && cnt > 0) || (lane == 31 && ph < pt));
+        if (m) {
+            const int src = __ffs(m) - 1;
+            int v = 0;
+            if (lane == src) {
+                volatile int *slot = nullptr;
+                if (lane == 31) {
+                    if (atomicCAS(&c->head, ph, ph + 1ULL) == ph) slot = &d.queue[(unsigned) ph & d.qmask];
+                } else if (atomicSub(&c->bcount[b], 1) > 0) {
+                    const unsigned long long h = atomicAdd(&c->bhead[b], 1ULL);
+                    slot = &ring[(unsigned) h & d.bqmask];
+                } else {
+                    atomicAdd(&c->bcount[b], 1);  // spent meanwhile: give the unit back
+                }
+                if (slot) {
+                    while ((v = *slot) == 0) {}
+                    *slot = 0;
+                }
+            }
+            v = __shfl_sync(full, v, src);
+            if (v) return v - 1;
+            continue;  // somebody else took it: look again
+        }
+        int stop = 0;
+        if (lane == 0) {
+            if (*(volatile int *) &c->done) stop = 1;
+            else if (fused0 && (d.ft->rank == 0 ? ld_sys(&d.ft->fc[0]->active) == 0
+                                                : (ld_sys(&d.ft->fc[d.ft->rank]->cmd) >> 2) != d.ft->fc[d.ft->rank]->seen_seq))
+                stop = 2;
+            else if ((++polls & 63u) == 0) {
+                // watchdog on GLOBAL progress: nothing pushed anywhere for timeout_ns
+                unsigned long long sum = *(volatile unsigned long long *) &c->tail;
+                for (int i = 0; i < d.nb; ++i) sum += *(volatile unsigned long long *) &c->btail[i];
+                if (t0 == 0 || sum != sum0) { t0 = globaltimer_ns(); sum0 = sum; }
+                else if (globaltimer_ns() - t0 > c->timeout_ns) { q_fail(d); stop = 1; }
+            }
+        }
+        stop = __shfl_sync(full, stop, 0);
+        if (stop) return -stop;
         __nanosleep(ns);
         if (ns < Q_SLEEP_MAX_NS) ns <<= 1;
     }
@@ -1171,7 +1184,7 @@ __global__ void __launch_bounds__(1024 / SW, SW == 4 ? 2 : 1) solver_kernel(Grid
 
     for (;;) {
         if (d.nb > 0 && tid < 32) {  // bucketed near queue: warp 0 pops together (never in fused mode)
-            const int t = q_pop_warp(d, tid);
+            const int t = q_pop_warp(d, tid, fused && blockIdx.x == 0);
             if (tid == 0) {
                 if (t >= 0) {
                     const int old = atomicExch(&d.state[t], ST_RUN);

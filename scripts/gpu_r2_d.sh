@@ -1,6 +1,18 @@
 #!/bin/bash
-# round 2, visit D (2 GPUs): the FUSED sharded planner — one process over both GPUs, then one process per GPU (CUDA IPC).
+# round 2 (1 GPU): upwind deferral (TASI_DEFER = margin in tile widths): parity, then timings
 mkdir -p gpurun_out
-PROBE_SETTINGS=1:1,2:1,4:1,8:1,16:1 timeout 600 python scripts/shard_probe.py 16384 0 2 > gpurun_out/shard_probe_fused_n2.jsonl 2> gpurun_out/shard_probe_fused_n2.err; echo "probe fused rc=$?"
-timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29517 bench.py --gpus 2 --workload bands --steps 2 --warmup 1 > gpurun_out/bands_fused_n2.json 2> gpurun_out/bands_fused_n2.err; echo "bands n2 rc=$?"
-cat gpurun_out/shard_probe_fused_n2.jsonl; tail -n 3 gpurun_out/shard_probe_fused_n2.err; cut -c1-3000 gpurun_out/bands_fused_n2.json; grep -v "^\[W\|^W1\|^\*\*\*\|OMP_NUM" gpurun_out/bands_fused_n2.err | tail -n 8
+export TASI_TIMEOUT_S=5
+TASI_DEFER=0.5 timeout 900 python -m pytest tests/test_gpu_parity.py tests/test_focus.py -m gpu -x -q > gpurun_out/pytest_defer.log 2>&1; echo "pytest defer rc=$?"; tail -n 3 gpurun_out/pytest_defer.log
+out=gpurun_out/defer_sweep.txt; : > $out
+run() { echo "== $* sizes $SIZES" >> $out; env "$@" timeout 600 python scripts/quick_bench.py $SIZES 2>&1 | python -c "
+import json,sys
+for l in sys.stdin:
+    try: d=json.loads(l)
+    except Exception: print(l.strip()[:200]); continue
+    tot=d['cyc_pop']+d['cyc_stage']+d['cyc_relax']+d['cyc_post']
+    print('kind %d N %5d ms %7.2f v/t %5.2f r/v %4.1f ev/el %5.1f cyc/visit %6.0f pop %.2f phases %d' % (d['kind'], d['N'], d['kernel_ms_solve'], d['visits_per_tile'], d['rounds_per_visit'], d['evals_per_elem'], tot/d['tile_visits'], d['cyc_pop']/tot, d['phases']))
+" >> $out; }
+SIZES="1024 4096 16384"
+run TASI_DEFER=-1
+for m in 0.25 0.5 1 2; do run TASI_DEFER=$m; done
+cat $out

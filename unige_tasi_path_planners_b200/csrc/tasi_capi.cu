@@ -68,6 +68,8 @@ struct tasi_planner {
     uint8_t *seed = nullptr;
     int *key = nullptr, *far = nullptr;
     int far_cap = 0;
+    int *rkey = nullptr; // upwind deferral (TASI_DEFER): claim keys of the running tiles
+    float defer_tiles = -1.0f;  // margin of the deferral in tile widths of mean cost (< 0: off)
     int *bq = nullptr;   // rings of the bucketed near queue (TASI_BUCKETS), nb x bqsize slots
     int nb = 30;
     unsigned bqsize = 0;
@@ -190,6 +192,9 @@ GridDesc make_desc(const tasi_planner *p) {
     // bucketed near queue: relax launches of an unsharded grid (run_solver switches it off for the invalidate launch)
     d.nb = active_rings(p);
     d.bq = p->bq;
+    d.rkey = p->rkey;
+    d.defer_margin = (d.nb > 0 && p->rkey && p->defer_tiles >= 0.0f)
+                         ? p->defer_tiles * (float) TS * p->mean_cost : -1.0f;
     d.bqmask = p->bqsize ? p->bqsize - 1 : 0;
     d.inv_bw = d.nb > 0 && d.delta > 0.0f ? (float) d.nb / d.delta : 0.0f;
     if (p->focus && !p->open_top && !p->open_bottom && p->band_rt == 0) {
@@ -207,8 +212,8 @@ GridDesc make_desc(const tasi_planner *p) {
 
 void free_grid(tasi_planner *p) {
     cudaFree(p->g_base); cudaFree(p->c_base); cudaFree(p->state); cudaFree(p->queue); cudaFree(p->seed);
-    cudaFree(p->stage); cudaFree(p->key); cudaFree(p->far); cudaFree(p->bq);
-    p->bq = nullptr;
+    cudaFree(p->stage); cudaFree(p->key); cudaFree(p->far); cudaFree(p->bq); cudaFree(p->rkey);
+    p->bq = nullptr; p->rkey = nullptr;
     p->key = nullptr; p->far = nullptr;
     p->g_base = nullptr; p->c_base = nullptr; p->state = nullptr; p->queue = nullptr; p->seed = nullptr;
     p->stage = nullptr;
@@ -332,6 +337,7 @@ int alloc_grid_arrays(tasi_planner *p, int EY, int nt, unsigned q) {
         CU_TRY(p, cudaMalloc(&p->bq, sizeof(int) * (size_t) bs * p->nb));
         CU_TRY(p, cudaMemsetAsync(p->bq, 0, sizeof(int) * (size_t) bs * p->nb, p->stream));
         p->bqsize = bs;
+        if (p->defer_tiles >= 0.0f) CU_TRY(p, cudaMalloc(&p->rkey, sizeof(int) * (size_t) nt));
     }
     if (tma_mode()) return make_tensor_maps(p);
     return TASI_OK;
@@ -443,7 +449,7 @@ int run_solver(tasi_planner *p, int mode, float *ms, bool resume = false, float 
     int rcs = ensure_cost_stats(p);
     if (rcs != TASI_OK) return rcs;
     GridDesc d = make_desc(p);
-    if (mode == 1) { d.n_focus = 0; d.nb = 0; }
+    if (mode == 1) { d.n_focus = 0; d.nb = 0; d.defer_margin = -1.0f; }
     static const bool repair_buckets = [] { const char *e = getenv("TASI_REPAIR_BUCKETS"); return !e || atoi(e) != 0; }();
     if (!p->fresh_plan && !repair_buckets) d.nb = 0;
     DevCtl z;
@@ -565,6 +571,7 @@ int tasi_create(int kind, int level, int device, tasi_planner **out) {
         double v = atof(e);
         if (v > 0) p->timeout_s = v;
     }
+    if (const char *e = getenv("TASI_DEFER")) p->defer_tiles = (float) atof(e);  // margin in tile widths; < 0 = off
     if (const char *e = getenv("TASI_BUCKETS")) {  // key-ordered rings of the near queue (0 = one FIFO ring)
         const int v = atoi(e);
         if (v >= 0 && v <= 30) p->nb = v;

@@ -483,7 +483,7 @@ int shard_fused_run(tasi_shard *s, int mode) {
         GridDesc d = make_desc(p);
         d.n_focus = 0;
         d.fmode = mode;
-        if (mode == 1) d.nb = 0;  // the invalidate launch has no order
+        if (mode == 1) { d.nb = 0; d.defer_margin = -1.0f; }  // the invalidate launch has no order
         const int nt = p->TX * p->TY;
         fused_rearm_kernel<<<1, 1, 0, p->stream>>>(d, m.fc, m.topo, mode, m.rank);
         if (mode == 0) seed_keys_kernel<<<std::min((nt + 7) / 8, p->num_sms * 8), 256, 0, p->stream>>>(d);

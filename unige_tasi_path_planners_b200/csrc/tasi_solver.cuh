@@ -35,7 +35,9 @@ constexpr int NTHREADS = 256;  // one thread per 1x4 strip of the tile
 constexpr int ST_DIRTY = 1;
 constexpr int ST_RUN = 2;
 constexpr int ST_FAR = 4;      // queued, but parked in the far pile (key >= current threshold)
-constexpr int ST_MASK = 7;     // the three state bits; bits ST_SHIFT.. of the same word hold the IN_* direction
+constexpr int ST_DEFER = 8;    // popped, found an upwind neighbour still at work, set aside until that one leaves (queued, in
+                               // no ring, still counted as pending)
+constexpr int ST_MASK = 15;    // the four state bits; bits ST_SHIFT.. of the same word hold the IN_* direction
 constexpr int ST_SHIFT = 8;    // bits (which halo sides changed since the tile was last staged)
 constexpr int INF_BITS = 0x7f800000;
 constexpr int GMARGIN = 32;    // columns of margin left of element/cell column 0 (keeps rows 128B aligned)
@@ -67,6 +69,7 @@ struct DevCtl {
     alignas(128) unsigned long long bhead[QB_MAX];
     alignas(128) unsigned long long btail[QB_MAX];
     alignas(128) int bcount[QB_MAX];  // published entries of each ring not yet claimed by a popper
+    unsigned long long deferred;      // tiles set aside by the upwind deferral
     // patch bookkeeping
     unsigned long long n_changed, n_raised, n_lowered_cells, n_seed_elems;
     unsigned long long halo_lowered;
@@ -117,6 +120,9 @@ struct GridDesc {
     int *bq;               // nb rings of bqmask + 1 slots (a power of two > tiles: a tile is queued at most once)
     unsigned bqmask;
     float inv_bw;          // nb / delta
+    // upwind deferral (TASI_DEFER, with the bucketed queue only): see "upwind deferral" below. margin < 0: off
+    float defer_margin;
+    int *rkey;             // TX*TY: the key a running tile was claimed with
 };
 
 // TMA staging (solver instances with TMA = 1, TASI_TMA=1): the two CUtensorMap (128 opaque bytes each) the kernel takes
@@ -176,6 +182,15 @@ __device__ inline void q_push_key(const GridDesc &d, int tile, int kbits) {
     __threadfence();
     atomicAdd(&d.ctl->bcount[b], 1);  // after the slot: a popper that wins a unit of the count finds its slot filled
                                       // (or about to be, by a pusher that already holds its ticket)
+}
+
+// back into its ring a tile that is already counted as pending (a deferred tile that is released)
+__device__ inline void q_repush(const GridDesc &d, int tile) {
+    const int b = max(bucket_of(d, *(volatile int *) &d.key[tile]), 0);
+    unsigned long long t = atomicAdd(&d.ctl->btail[b], 1ULL);
+    atomicExch(&d.bq[(size_t) b * (d.bqmask + 1u) + ((unsigned) t & d.bqmask)], tile + 1);
+    __threadfence();
+    atomicAdd(&d.ctl->bcount[b], 1);
 }
 
 __device__ inline void q_push(const GridDesc &d, int tile) {
@@ -247,11 +262,16 @@ __device__ inline void far_append(const GridDesc &d, int tile) {
 }
 
 __device__ inline void activate(const GridDesc &d, int tile, int kbits, int dirbit) {
-    atomicMin(&d.key[tile], kbits);  // may land after the state bit: a stale low key only makes the tile look due
+    const int oldk = atomicMin(&d.key[tile], kbits);  // may land after the state bit: a stale low key only makes the tile look due
     const bool near = kbits < cur_thr_bits(d);
     // one atomic both flags the tile and records which of its halo sides changed (bits ST_SHIFT..)
     const int old = atomicOr(&d.state[tile], ST_DIRTY | (dirbit << ST_SHIFT));
     const int st = old & ST_MASK;
+    if ((st & ST_DEFER) && kbits < oldk) {
+        // set aside with a higher key: what it waited for may now wait for IT, so it goes back into the rings
+        if (atomicAnd(&d.state[tile], ~ST_DEFER) & ST_DEFER) q_repush(d, tile);
+        return;
+    }
     if (st == 0) {  // it was idle: ours to queue
         if (near) {
             q_push_key(d, tile, kbits);
@@ -419,10 +439,22 @@ __device__ __forceinline__ void fused_rank_idles(const GridDesc &d) { atomicAdd_
 // activate() on a tile of another rank `r` (its GridDesc, peer-mapped). `near` is judged by OUR threshold: thresholds
 // are global in this mode.
 __device__ inline void activate_remote(const GridDesc &d, const GridDesc &r, FusedCtl *rfc, int tile, int kbits, int dirbit) {
-    atomicMin_system(&r.key[tile], kbits);
+    const int oldk = atomicMin_system(&r.key[tile], kbits);
     const bool near = kbits < cur_thr_bits(d);
     const int old = atomicOr_system(&r.state[tile], ST_DIRTY | (dirbit << ST_SHIFT));
     const int st = old & ST_MASK;
+    if ((st & ST_DEFER) && kbits < oldk) {
+        // set aside over there with a higher key (upwind deferral): back into its rings, it is counted as pending already
+        if ((atomicAnd_system(&r.state[tile], ~ST_DEFER) & ST_DEFER) && r.bq) {
+            const int b = max(bucket_of(d, kbits), 0);
+            const unsigned long long t = atomicAdd_system(&r.ctl->btail[b], 1ULL);
+            atomicExch_system(&r.bq[(size_t) b * (r.bqmask + 1u) + ((unsigned) t & r.bqmask)], tile + 1);
+            fence_sys();
+            atomicAdd_system(&r.ctl->bcount[b], 1);
+        }
+        atomicAdd(&d.ft->fc[d.ft->rank]->tx, 1ULL);
+        return;
+    }
     bool push = false;
     if (st == 0) {
         if (near) push = true;
@@ -715,6 +747,69 @@ __device__ inline int q_pop_warp(const GridDesc &d, int lane, bool fused0) {
         __nanosleep(ns);
         if (ns < Q_SLEEP_MAX_NS) ns <<= 1;
     }
+}
+
+// ---- upwind deferral (TASI_DEFER; bucketed queue, unsharded grids) --------------------------------------------------------
+// A tile visited while an upwind neighbour is still queued or running works on a border that is about to change, and is
+// visited again when it has: that is most of the 8-17 visits a tile gets. Here a popped tile looks at its 8 neighbours
+// first; if one of them is queued or running with a key lower than its own by more than `defer_margin` (about half a tile
+// width of cost, so that tiles side by side on the same front do not wait for each other), it is set aside: ST_DEFER in
+// its state word, in no ring, still counted as pending. It returns to the rings when (a) a neighbour leaves its visit (the
+// leaving CTA releases every deferred neighbour) or (b) an activation lowers its key (what it waited for may now have to
+// wait for it). "Lower by a margin" is acyclic and the tile with the lowest key never waits, so the schedule cannot stall;
+// both hand-overs go through one atomic on the state word of the deferred tile (whoever clears the bit owns the push).
+__device__ __forceinline__ bool defer_blocked(const GridDesc &d, int t, int lane) {
+    const int mykey = *(volatile int *) &d.key[t];
+    bool blocked = false;
+    if (lane < 8 && mykey != INF_BITS) {
+        const float lim = __int_as_float(mykey) - d.defer_margin;
+        const int tx = t / d.TY, ty = t - tx * d.TY;
+        const int dx = (0x31 >> lane & 1) ? -1 : ((0xc2 >> lane & 1) ? 1 : 0);
+        const int dy = (0x54 >> lane & 1) ? -1 : ((0xa8 >> lane & 1) ? 1 : 0);
+        const int nx = tx + dx, ny = ty + dy;
+        if (lim > 0.0f && nx >= 0 && nx < d.TX && ny >= 0 && ny < d.TY && !dead_tile_row(d, nx)) {
+            const int n = nx * d.TY + ny;
+            const int st = *(volatile int *) &d.state[n];
+            if ((st & (ST_DIRTY | ST_RUN)) && !(st & ST_FAR)) {
+                int nk = INF_BITS;
+                if (st & ST_RUN) nk = *(volatile int *) &d.rkey[n];
+                if (st & ST_DIRTY) nk = min(nk, *(volatile int *) &d.key[n]);
+                blocked = nk < __float_as_int(lim);
+            }
+        }
+    }
+    return __any_sync(0xffffffffu, blocked);
+}
+
+// The popped tile t: true = run it; false = it was set aside (or a releaser has taken it over): pop another. Warp 0.
+__device__ inline bool defer_or_run(const GridDesc &d, int t, int lane) {
+    if (!defer_blocked(d, t, lane)) return true;
+    if (lane == 0) {
+        atomicOr(&d.state[t], ST_DEFER);
+        fence_gpu();
+    }
+    __syncwarp();
+    int run = 0;
+    if (!defer_blocked(d, t, lane)) {
+        // whatever blocked it has left meanwhile (and may or may not have seen the bit): whoever clears it owns the tile
+        if (lane == 0) run = (atomicAnd(&d.state[t], ~ST_DEFER) & ST_DEFER) ? 1 : 0;
+        run = __shfl_sync(0xffffffffu, run, 0);
+    } else if (lane == 0) {
+        atomicAdd(&d.ctl->deferred, 1ULL);
+    }
+    return run != 0;
+}
+
+// A visit has ended (the tile is idle or parked again): release the deferred neighbours. Lanes 0..7 of one warp.
+__device__ __forceinline__ void release_deferred(const GridDesc &d, int tile, int lane) {
+    if (lane >= 8) return;
+    const int tx = tile / d.TY, ty = tile - tx * d.TY;
+    const int dx = (0x31 >> lane & 1) ? -1 : ((0xc2 >> lane & 1) ? 1 : 0);
+    const int dy = (0x54 >> lane & 1) ? -1 : ((0xa8 >> lane & 1) ? 1 : 0);
+    const int nx = tx + dx, ny = ty + dy;
+    if (nx < 0 || nx >= d.TX || ny < 0 || ny >= d.TY || dead_tile_row(d, nx)) return;
+    const int n = nx * d.TY + ny;
+    if ((*(volatile int *) &d.state[n] & ST_DEFER) && (atomicAnd(&d.state[n], ~ST_DEFER) & ST_DEFER)) q_repush(d, n);
 }
 
 // ---- in-tile relaxation: strips with a register copy of their neighbourhood ------------------------------------------
@@ -1183,10 +1278,14 @@ __global__ void __launch_bounds__(1024 / SW, SW == 4 ? 2 : 1) solver_kernel(Grid
     }
 
     for (;;) {
-        if (d.nb > 0 && tid < 32) {  // bucketed near queue: warp 0 pops together (never in fused mode)
-            const int t = q_pop_warp(d, tid, fused && blockIdx.x == 0);
+        if (d.nb > 0 && tid < 32) {  // bucketed near queue: warp 0 pops together
+            int t;
+            do {
+                t = q_pop_warp(d, tid, fused && blockIdx.x == 0);
+            } while (t >= 0 && d.defer_margin >= 0.0f && !defer_or_run(d, t, tid));
             if (tid == 0) {
                 if (t >= 0) {
+                    if (d.defer_margin >= 0.0f) d.rkey[t] = *(volatile int *) &d.key[t];
                     const int old = atomicExch(&d.state[t], ST_RUN);
                     s_inmask = old >> ST_SHIFT;
                     atomicExch(&d.key[t], INF_BITS);
@@ -1422,6 +1521,7 @@ __global__ void __launch_bounds__(1024 / SW, SW == 4 ? 2 : 1) solver_kernel(Grid
                     const int kk = atomicMin(&d.key[tile], INF_BITS);  // atomic read
                     if (kk < cur_thr_bits(d) || kk == INF_BITS) {
                         // due now (or its key was consumed with the previous staging): go round again
+                        if (d.nb > 0 && d.defer_margin >= 0.0f && kk != INF_BITS) d.rkey[tile] = kk;
                         old = atomicExch(&d.state[tile], ST_RUN);
                         s_inmask = old >> ST_SHIFT;
                         atomicExch(&d.key[tile], INF_BITS);
@@ -1437,6 +1537,10 @@ __global__ void __launch_bounds__(1024 / SW, SW == 4 ? 2 : 1) solver_kernel(Grid
             }
             __syncthreads();
             again = s_again != 0;
+            if (!again && d.nb > 0 && d.defer_margin >= 0.0f && tid >= 32 && tid < 40) {
+                fence_gpu();  // our state word left RUN before we look at the neighbours' (see defer_or_run)
+                release_deferred(d, tile, tid - 32);
+            }
             c1 = clock64(); c_post += c1 - c0; c0 = c1;
         } while (again);
 

@@ -193,6 +193,8 @@ GridDesc make_desc(const tasi_planner *p) {
     d.nb = active_rings(p);
     d.bq = p->bq;
     d.rkey = p->rkey;
+    static const int chain = [] { const char *e = getenv("TASI_CHAIN"); return e ? atoi(e) : 0; }();
+    d.chain = chain;
     d.defer_margin = (d.nb > 0 && p->rkey && p->defer_tiles >= 0.0f)
                          ? p->defer_tiles * (float) TS * p->mean_cost : -1.0f;
     d.bqmask = p->bqsize ? p->bqsize - 1 : 0;

@@ -123,6 +123,7 @@ struct GridDesc {
     // upwind deferral (TASI_DEFER, with the bucketed queue only): see "upwind deferral" below. margin < 0: off
     float defer_margin;
     int *rkey;             // TX*TY: the key a running tile was claimed with
+    int chain;             // TASI_CHAIN: a CTA goes on with the lowest-keyed neighbour it has just activated (see solver_kernel)
 };
 
 // TMA staging (solver instances with TMA = 1, TASI_TMA=1): the two CUtensorMap (128 opaque bytes each) the kernel takes
@@ -261,7 +262,8 @@ __device__ inline void far_append(const GridDesc &d, int tile) {
     }
 }
 
-__device__ inline void activate(const GridDesc &d, int tile, int kbits, int dirbit) {
+// hold: if the tile was idle and is due now, do NOT queue it but return true — the caller queues it or runs it itself
+__device__ inline bool activate(const GridDesc &d, int tile, int kbits, int dirbit, bool hold = false) {
     const int oldk = atomicMin(&d.key[tile], kbits);  // may land after the state bit: a stale low key only makes the tile look due
     const bool near = kbits < cur_thr_bits(d);
     // one atomic both flags the tile and records which of its halo sides changed (bits ST_SHIFT..)
@@ -270,10 +272,11 @@ __device__ inline void activate(const GridDesc &d, int tile, int kbits, int dirb
     if ((st & ST_DEFER) && kbits < oldk) {
         // set aside with a higher key: what it waited for may now wait for IT, so it goes back into the rings
         if (atomicAnd(&d.state[tile], ~ST_DEFER) & ST_DEFER) q_repush(d, tile);
-        return;
+        return false;
     }
     if (st == 0) {  // it was idle: ours to queue
         if (near) {
+            if (hold) return true;
             q_push_key(d, tile, kbits);
             atomicAdd(&d.ctl->pushes, 1ULL);
         } else {
@@ -287,6 +290,7 @@ __device__ inline void activate(const GridDesc &d, int tile, int kbits, int dirb
             atomicAdd(&d.ctl->pushes, 1ULL);
         }
     }
+    return false;
 }
 
 // The queue has drained and no tile is running: raise the threshold to (lowest parked key + delta) and move
@@ -1274,8 +1278,9 @@ __global__ void __launch_bounds__(1024 / SW, SW == 4 ? 2 : 1) solver_kernel(Grid
     __shared__ float sg[(TS + 2) * GP];   // values, rows/cols -1..32
     __shared__ float sc[(TS + 1) * CP];   // cell costs as float, INF = obstacle
     __shared__ int s_tile, s_inmask, s_again, s_adv;
+    __shared__ int s_chain, s_chain_key;  // chaining: the neighbour this CTA goes on with (-1: none)
     __shared__ int s_next;                // pop-ahead: the tile taken from the rings during the previous visit's epilogue (-1: none)
-    if (threadIdx.x == 0) s_next = -1;
+    if (threadIdx.x == 0) { s_next = -1; s_chain = -1; }
     __shared__ int s_kmin[8];             // per neighbour direction: lowest changed value it will read (bits)
     __shared__ int s_red[MAX_WARPS];
     __shared__ int s_cmd[2];              // fused mode: command being served by CTA 0
@@ -1316,8 +1321,11 @@ __global__ void __launch_bounds__(1024 / SW, SW == 4 ? 2 : 1) solver_kernel(Grid
 
     for (;;) {
         if (d.nb > 0 && tid < 32) {  // bucketed near queue: warp 0 pops together
-            int t = -1;  // taken ahead during the last epilogue?
-            if (tid == 0) { t = s_next; s_next = -1; }
+            int t = -1;  // kept from the last visit (chaining), or taken ahead during its epilogue?
+            if (tid == 0) {
+                if (s_chain >= 0) t = s_chain;  // (reset after the barrier below: the other threads still read it)
+                else { t = s_next; s_next = -1; }
+            }
             t = __shfl_sync(0xffffffffu, t, 0);
             if (t >= 0 && d.defer_margin >= 0.0f && !defer_or_run(d, t, tid)) t = -1;
             if (t < 0) {
@@ -1349,6 +1357,7 @@ __global__ void __launch_bounds__(1024 / SW, SW == 4 ? 2 : 1) solver_kernel(Grid
         }
         if (tid < 8) s_kmin[tid] = INF_BITS;
         __syncthreads();
+        if (tid == 0) s_chain = -1;
         const int tile = s_tile;
         if (tile == -2) {  // fused mode, CTA 0: a phase boundary / a command of the coordinator
             fused_service(d, s_red, s_cmd, tid);
@@ -1543,9 +1552,26 @@ __global__ void __launch_bounds__(1024 / SW, SW == 4 ? 2 : 1) solver_kernel(Grid
                 const int seen_as = (IN_S << 0) * (tid == 0) + IN_N * (tid == 1) + IN_E * (tid == 2) + IN_W * (tid == 3) +
                                     IN_SE * (tid == 4) + IN_SW * (tid == 5) + IN_NE * (tid == 6) + IN_NW * (tid == 7);
                 const int nx = tx + dx, ny = ty + dy;
+                const bool chain = MODE == 0 && d.chain && d.nb > 0 && !fused && d.defer_margin < 0.0f;
+                bool held = false;
                 if (k != INF_BITS && nx >= 0 && nx < d.TX && ny >= 0 && ny < d.TY && !dead_tile_row(d, nx))
-                    activate(d, nx * d.TY + ny, k, seen_as);
-                else if (fused && k != INF_BITS && dx != 0 && ny >= 0 && ny < d.TY) {
+                    held = activate(d, nx * d.TY + ny, k, seen_as, chain);
+                if (chain) {
+                    // chaining: of the neighbours this visit woke from idle, the CTA keeps the one with the lowest key for
+                    // itself (it is not queued: no push, no pop; the pending count of the ending visit passes to it); the
+                    // others go to the rings
+                    const unsigned hm = __ballot_sync(0xffu, held);
+                    int best = -1, bk = INF_BITS;
+                    for (int l = 0; l < 8; ++l) {
+                        const int kl = __shfl_sync(0xffu, k, l);
+                        if (((hm >> l) & 1u) && kl < bk) { bk = kl; best = l; }
+                    }
+                    if (held && tid != best) {
+                        q_push_key(d, nx * d.TY + ny, k);
+                        atomicAdd(&d.ctl->pushes, 1ULL);
+                    }
+                    if (tid == best) { s_chain = nx * d.TY + ny; s_chain_key = k; }
+                } else if (fused && k != INF_BITS && dx != 0 && ny >= 0 && ny < d.TY) {
                     // across a band edge: the tile belongs to a neighbour rank
                     const FusedTopo &ft = *d.ft;
                     const int bp = d.band_rt + 1, bt = tx % bp, jb = tx / bp, gb = jb * ft.world + ft.rank;
@@ -1585,6 +1611,11 @@ __global__ void __launch_bounds__(1024 / SW, SW == 4 ? 2 : 1) solver_kernel(Grid
             }
             __syncthreads();
             again = s_again != 0;
+            if (again && tid == 0 && s_chain >= 0) {  // the visit goes on: the kept neighbour goes to the rings after all
+                q_push_key(d, s_chain, s_chain_key);
+                atomicAdd(&d.ctl->pushes, 1ULL);
+                s_chain = -1;
+            }
             if (!again && d.nb > 0 && d.defer_margin >= 0.0f && tid >= 32 && tid < 40) {
                 fence_gpu();  // our state word left RUN before we look at the neighbours' (see defer_or_run)
                 release_deferred(d, tile, tid - 32);
@@ -1598,6 +1629,7 @@ __global__ void __launch_bounds__(1024 / SW, SW == 4 ? 2 : 1) solver_kernel(Grid
             if (tid == 0 && atomicSub(&d.ctl->pending, 1) == 1) fused_rank_idles(d);
             continue;
         }
+        if (s_chain >= 0) continue;  // chaining: the pending count of this visit passes to the kept neighbour
         if (tid == 0) s_adv = (atomicSub(&d.ctl->pending, 1) == 1) ? 1 : 0;
         drain_and_advance(d, s_red, &s_adv, tid);
     }

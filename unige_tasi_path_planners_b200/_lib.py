@@ -9,7 +9,7 @@ import os
 import numpy as np
 
 PKG = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(PKG, "libtasi_gpu.so")
+LIB_PATH = os.environ.get("TASI_GPU_LIB") or os.path.join(PKG, "libtasi_gpu.so")  # (override: development builds)
 
 OK = 0
 LOOP_OK = 0

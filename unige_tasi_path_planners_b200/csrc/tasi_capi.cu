@@ -474,7 +474,15 @@ int run_solver(tasi_planner *p, int mode, float *ms, bool resume = false, float 
     if (ordered) seed_keys_kernel<<<std::min((nt + 7) / 8, p->num_sms * 8), 256, 0, p->stream>>>(d);
     enqueue_seeds_kernel<<<std::min((nt + 255) / 256, 1024), 256, 0, p->stream>>>(d, ordered);
     arm_solver_kernel<<<1, 1, 0, p->stream>>>(d);
-    const int nblocks = (p->max_blocks > 0 && p->max_blocks < p->solver_blocks) ? p->max_blocks : p->solver_blocks;
+    int nblocks = (p->max_blocks > 0 && p->max_blocks < p->solver_blocks) ? p->max_blocks : p->solver_blocks;
+    static const bool own_occ = [] { const char *e = getenv("TASI_OWN_OCC"); return e && atoi(e) != 0; }();
+    if (own_occ && p->max_blocks <= 0) {  // development: as many CTAs as THIS instance fits per SM (all must be resident)
+        int occ = 0;
+        CU_TRY(p, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, pick_solver(p->kind, mode, p->strip, compact_for(p)),
+                                                                TS * TS / p->strip, 0));
+        nblocks = std::min(std::max(occ, 1) * p->num_sms, nt);
+        p->stats.solver_blocks = nblocks;
+    }
     pick_solver(p->kind, mode, p->strip, compact_for(p))<<<nblocks, TS * TS / p->strip, 0, p->stream>>>(d, p->tm);
     CU_TRY(p, cudaGetLastError());
     CU_TRY(p, cudaEventRecord(p->ev1, p->stream));

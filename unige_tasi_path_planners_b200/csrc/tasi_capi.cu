@@ -584,7 +584,7 @@ int tasi_create(int kind, int level, int device, tasi_planner **out) {
     if (const char *e = getenv("TASI_DEFER")) p->defer_tiles = (float) atof(e);  // margin in tile widths; < 0 = off
     if (const char *e = getenv("TASI_BUCKETS")) {  // key-ordered rings of the near queue (0 = one FIFO ring)
         const int v = atoi(e);
-        if (v >= 0 && v <= 30) p->nb = v;
+        if (v >= 0 && v <= 62) p->nb = v;
     }
     if (const char *e = getenv("TASI_DELTA_FACTOR")) {  // fixed factor; <= 0: no ordering
         p->delta_factor = (float) atof(e);

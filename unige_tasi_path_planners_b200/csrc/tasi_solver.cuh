@@ -42,7 +42,8 @@ constexpr int ST_SHIFT = 8;    // bits (which halo sides changed since the tile 
 constexpr int INF_BITS = 0x7f800000;
 constexpr int GMARGIN = 32;    // columns of margin left of element/cell column 0 (keeps rows 128B aligned)
 
-constexpr int QB_MAX = 32;     // size of the ring counter arrays of the bucketed near queue (at most 30 rings: one lane each)
+constexpr int QB_MAX = 64;     // size of the ring counter arrays of the bucketed near queue (at most 62 rings: two per lane of
+                               // the popping warp, lane 31 watches the plain ring)
 
 struct DevCtl {
     unsigned long long head, tail;  // ticket counters of the work queue
@@ -687,8 +688,8 @@ __device__ inline int q_pop_fused(const GridDesc &d, unsigned long long *ticket)
     }
 }
 
-// q_pop of the bucketed near queue, called by the 32 lanes of warp 0 together: lane b looks at the count of ring b (one
-// coalesced read per poll), the lowest ring with entries is tried: a unit of its count is taken with an unconditional
+// q_pop of the bucketed near queue, called by the 32 lanes of warp 0 together: lane b looks at the counts of rings b and
+// b + 31 (coalesced reads), the lowest ring with entries is tried: a unit of its count is taken with an unconditional
 // atomic (given back if the count was already spent — no CAS loop, so hundreds of CTAs do not serialise on one word),
 // then a ticket of its head, whose slot is filled or about to be. Nobody commits to a ring that may never be fed again.
 // Lane 31 watches the plain ring (entries queued without an order before the launch). Returns the same value to every lane.
@@ -696,30 +697,31 @@ __device__ inline int q_pop_fused(const GridDesc &d, unsigned long long *ticket)
 __device__ inline int q_pop_warp(const GridDesc &d, int lane, bool fused0) {
     DevCtl *c = d.ctl;
     const unsigned full = 0xffffffffu;
-    const int b = lane & (QB_MAX - 1);
-    int *ring = d.bq + (size_t) b * (d.bqmask + 1u);
-    const bool mine = lane < d.nb;
+    const bool m0 = lane < 31 && lane < d.nb, m1 = lane < 31 && lane + 31 < d.nb;  // rings lane and lane + 31
     unsigned long long t0 = 0, sum0 = 0;
     unsigned ns = 32, polls = 0;
     for (;;) {
-        int cnt = 0;
+        int cnt0 = 0, cnt1 = 0;
         unsigned long long ph = 0, pt = 0;
-        if (mine) cnt = *(volatile int *) &c->bcount[b];
+        if (m0) cnt0 = *(volatile int *) &c->bcount[lane];
+        if (m1) cnt1 = *(volatile int *) &c->bcount[lane + 31];
         if (lane == 31) {
             ph = *(volatile unsigned long long *) &c->head;
             pt = *(volatile unsigned long long *) &c->tail;
         }
-        const unsigned m = __ballot_sync(full, (mine && cnt > 0) || (lane == 31 && ph < pt));
-        if (m) {
-            const int src = __ffs(m) - 1;
+        const unsigned ma = __ballot_sync(full, cnt0 > 0), mb = __ballot_sync(full, cnt1 > 0);
+        const unsigned mp = __ballot_sync(full, lane == 31 && ph < pt);
+        if (ma | mb | mp) {
+            const int src = ma ? __ffs(ma) - 1 : (mb ? __ffs(mb) - 1 : 31);
+            const int b = ma ? src : src + 31;
             int v = 0;
             if (lane == src) {
                 volatile int *slot = nullptr;
-                if (lane == 31) {
+                if (!(ma | mb)) {
                     if (atomicCAS(&c->head, ph, ph + 1ULL) == ph) slot = &d.queue[(unsigned) ph & d.qmask];
                 } else if (atomicSub(&c->bcount[b], 1) > 0) {
                     const unsigned long long h = atomicAdd(&c->bhead[b], 1ULL);
-                    slot = &ring[(unsigned) h & d.bqmask];
+                    slot = &d.bq[(size_t) b * (d.bqmask + 1u) + ((unsigned) h & d.bqmask)];
                 } else {
                     atomicAdd(&c->bcount[b], 1);  // spent meanwhile: give the unit back
                 }
@@ -751,37 +753,6 @@ __device__ inline int q_pop_warp(const GridDesc &d, int lane, bool fused0) {
         __nanosleep(ns);
         if (ns < Q_SLEEP_MAX_NS) ns <<= 1;
     }
-}
-
-// One look at the rings without waiting (all 32 lanes of a warp): a tile, or -1 if nothing is queued right now. Used to
-// take the next tile while the current one is still being written back and its neighbours activated (pop-ahead).
-__device__ inline int q_try_pop_warp(const GridDesc &d, int lane) {
-    DevCtl *c = d.ctl;
-    const unsigned full = 0xffffffffu;
-    const int b = lane & (QB_MAX - 1);
-    int *ring = d.bq + (size_t) b * (d.bqmask + 1u);
-    const bool mine = lane < d.nb;
-    for (int attempt = 0; attempt < 3; ++attempt) {
-        int cnt = 0;
-        if (mine) cnt = *(volatile int *) &c->bcount[b];
-        const unsigned m = __ballot_sync(full, mine && cnt > 0);
-        if (!m) return -1;
-        const int src = __ffs(m) - 1;
-        int v = 0;
-        if (lane == src) {
-            if (atomicSub(&c->bcount[b], 1) > 0) {
-                const unsigned long long h = atomicAdd(&c->bhead[b], 1ULL);
-                volatile int *slot = &ring[(unsigned) h & d.bqmask];
-                while ((v = *slot) == 0) {}
-                *slot = 0;
-            } else {
-                atomicAdd(&c->bcount[b], 1);
-            }
-        }
-        v = __shfl_sync(full, v, src);
-        if (v) return v - 1;
-    }
-    return -1;
 }
 
 // ---- upwind deferral (TASI_DEFER; bucketed queue, unsharded grids) --------------------------------------------------------
@@ -874,10 +845,6 @@ constexpr int MAX_WARPS = 16;     // per CTA, over the kernel instances (SW = 2:
 #endif
 #ifndef UPWIND_FILTER
 #define UPWIND_FILTER 1
-#endif
-#ifndef POP_AHEAD
-#define POP_AHEAD 0  // measured: the tile taken ahead misses the activations of the visit that is ending (they are the lowest keys)
-                     // and is held while other CTAs idle: visits per tile 16.9 -> 23.8, MS-DFM 4096^2 14.6 -> 20.2 ms
 #endif
 template <int KIND, int SW>
 struct SweepsPerBarrier { static constexpr int value = (KIND == TASI_KIND_DFM) ? RPB_DFM : (SW == 2 ? 2 : 1); };
@@ -1283,8 +1250,7 @@ solver_kernel(GridDesc d, const __grid_constant__ TmaMaps tm) {
     __shared__ float sc[(TS + 1) * CP];   // cell costs as float, INF = obstacle
     __shared__ int s_tile, s_inmask, s_again, s_adv;
     __shared__ int s_chain, s_chain_key;  // chaining: the neighbour this CTA goes on with (-1: none)
-    __shared__ int s_next;                // pop-ahead: the tile taken from the rings during the previous visit's epilogue (-1: none)
-    if (threadIdx.x == 0) { s_next = -1; s_chain = -1; }
+    if (threadIdx.x == 0) s_chain = -1;
     __shared__ int s_kmin[8];             // per neighbour direction: lowest changed value it will read (bits)
     __shared__ int s_red[MAX_WARPS];
     __shared__ int s_cmd[2];              // fused mode: command being served by CTA 0
@@ -1325,11 +1291,8 @@ solver_kernel(GridDesc d, const __grid_constant__ TmaMaps tm) {
 
     for (;;) {
         if (d.nb > 0 && tid < 32) {  // bucketed near queue: warp 0 pops together
-            int t = -1;  // kept from the last visit (chaining), or taken ahead during its epilogue?
-            if (tid == 0) {
-                if (s_chain >= 0) t = s_chain;  // (reset after the barrier below: the other threads still read it)
-                else { t = s_next; s_next = -1; }
-            }
+            int t = -1;  // kept from the last visit (chaining)? (reset after the barrier below: the other threads still read it)
+            if (tid == 0 && s_chain >= 0) t = s_chain;
             t = __shfl_sync(0xffffffffu, t, 0);
             if (t >= 0 && d.defer_margin >= 0.0f && !defer_or_run(d, t, tid)) t = -1;
             if (t < 0) {
@@ -1533,12 +1496,6 @@ solver_kernel(GridDesc d, const __grid_constant__ TmaMaps tm) {
             __syncthreads();
             // the CTA's write-back (ordered by the barrier) before the flags below; the leaving thread sits in another
             // warp than the activating ones, so its atomics overlap theirs instead of following them
-            // pop-ahead: warp 2 takes the next tile from the rings (if one is queued) while warps 0 and 1 activate the
-            // neighbours and leave this one — the 3-4 dependent L2 round trips of a pop overlap the epilogue
-            if (POP_AHEAD && d.nb > 0 && tid >= 64 && tid < 96 && *(volatile int *) &s_next < 0) {
-                const int nt = q_try_pop_warp(d, tid - 64);
-                if (tid == 64) s_next = nt;
-            }
             if (tid < 8 || tid == LEAVE_TID) {
                 // fused mode: only a tile on a band border stores into another GPU's memory and raises its flags; the
                 // values of an interior tile are read by CTAs of this GPU alone, for which the device-scope fence does

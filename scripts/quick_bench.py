@@ -17,6 +17,8 @@ for N in sizes:
         p.synth_map(1, N, N, 0, 10, start, goal)
         p.set_start(*start)
         p.set_goal(*goal)
+        if os.environ.get("QUICK_BLOCKS"):
+            p.set_solver_blocks(int(os.environ["QUICK_BLOCKS"]))
         best = None
         for it in range(3):
             p.reset()

@@ -233,22 +233,23 @@ solver_fn pick_solver_sw(int kind, int mode) {
         default: return solver_kernel<TASI_KIND_MFD, 1, SW, 0>;
     }
 }
-// How the relax visits evaluate: 0 strips (relax_tile), 1 compacted over the CTA (relax_tile_compact), 2 compacted
-// inside each warp (relax_tile_wcompact). TASI_COMPACT=0|1|2 overrides the per-planner default.
+// How the relax visits evaluate: 0 strips (relax_tile), 1 compacted over the CTA, dirty elements found by scanning the
+// windows (relax_tile_compact), 2 compacted inside each warp (relax_tile_wcompact), 3 compacted over the CTA, dirty marks
+// pushed by the evaluations (relax_tile_push). TASI_COMPACT=0|1|2|3 overrides the per-planner default.
 inline int compact_mode(int kind) {
     static const int env = [] {
         const char *e = getenv("TASI_COMPACT");
         return e ? atoi(e) : -1;
     }();
-    if (env >= 0 && env <= 2) return env;
-    return kind == TASI_FD ? 1 : 0;
+    if (env >= 0 && env <= 3) return env;
+    return kind == TASI_FD ? 3 : 0;
 }
 // ... per launch: MFD* gains from the CTA list only where the solve is throughput-bound — the initial plan of a large grid
 // (16384^2: 134.8 -> 130.2 ms; 4096^2 loses, 17.7 -> 19.9 ms, and so does the small active region of a replan)
 inline int compact_for(const tasi_planner *p) {
     const int c = compact_mode(p->kind);
     static const bool fixed = getenv("TASI_COMPACT") != nullptr;
-    if (!fixed && p->kind == TASI_MFD && p->fresh_plan && (int64_t) p->TX * p->TY >= 50000 && p->band_rt == 0) return 1;
+    if (!fixed && p->kind == TASI_MFD && p->fresh_plan && (int64_t) p->TX * p->TY >= 50000 && p->band_rt == 0) return 3;
     return c;
 }
 // TASI_TMA=1: the relax instances stage their tiles with cp.async.bulk.tensor.2d instead of vector loads (strips only;
@@ -272,6 +273,7 @@ solver_fn pick_solver_tma(int kind) {
 solver_fn pick_solver(int kind, int mode, int strip, int cmp = -1) {
     if (tma_mode() && mode == 0) return strip == 2 ? pick_solver_tma<2>(kind) : pick_solver_tma<4>(kind);
     switch (cmp >= 0 ? cmp : compact_mode(kind)) {
+        case 3: return strip == 2 ? pick_solver_sw<2, 3>(kind, mode) : pick_solver_sw<4, 3>(kind, mode);
         case 2: return strip == 2 ? pick_solver_sw<2, 2>(kind, mode) : pick_solver_sw<4, 2>(kind, mode);
         case 1: return strip == 2 ? pick_solver_sw<2, 1>(kind, mode) : pick_solver_sw<4, 1>(kind, mode);
         default: return strip == 2 ? pick_solver_sw<2, 0>(kind, mode) : pick_solver_sw<4, 0>(kind, mode);
@@ -384,7 +386,7 @@ int alloc_grid_dims(tasi_planner *p, int W, int rows, int EX, int EY) {
     CU_TRY(p, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&dev_blocks1, pick_solver(p->kind, 1, strip), nthreads, 0));
     if (dev_blocks1 < dev_blocks) dev_blocks = dev_blocks1;
     if (p->kind == TASI_MFD) {  // compact_for() may pick the CTA-list instance for an initial plan
-        CU_TRY(p, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&dev_blocks1, pick_solver(p->kind, 0, strip, 1), nthreads, 0));
+        CU_TRY(p, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&dev_blocks1, pick_solver(p->kind, 0, strip, 3), nthreads, 0));
         if (dev_blocks1 < dev_blocks) dev_blocks = dev_blocks1;
     }
     if (dev_blocks < 1) { p->err = "solver kernel does not fit on an SM"; return TASI_ERR_CUDA; }

@@ -1096,6 +1096,121 @@ __device__ __forceinline__ int relax_tile_compact(float *sg, const float *sc, un
     return cnt_changed;
 }
 
+// ---- in-tile relaxation, compacted, dirty marks pushed by the evaluations (CMP = 3) ------------------------------------
+// relax_tile_compact finds the dirty elements of a round by having EVERY thread re-read and compare the 3 x (SW + 2)
+// window of its strip: about as many instructions per round as the evaluations themselves once the lists are short
+// (FD* 16384^2: ~110 evaluations per round). Here the evaluation that lowers an element marks the neighbours the new
+// value can help — those whose value it has just read as higher (it holds all eight in registers) — in a byte map in
+// shared memory; the owner of a strip reads its SW bytes (one load), clears them and puts the marked elements on the
+// round's list. A second byte map records which elements changed during the visit (what the owner writes back). Marks are
+// plain byte stores of 1 (races are benign); a value read stale is read as higher, so a mark can only be superfluous,
+// never missing: the fixed point is the one of the other relaxations (bit-exact). Two CTA barriers per round, as CMP = 1.
+template <int KIND, int SW>
+__device__ __forceinline__ int relax_tile_push(float *sg, const float *sc, unsigned short *s_list, int *s_n,
+                                               unsigned char *s_dirty, unsigned char *s_chgmap, int inmask, int row, int col0,
+                                               int rlim, int clim, int pin_r, int pin_c, float (&w)[WIN_R][SW + 2],
+                                               unsigned &chg, unsigned &iters, unsigned &evals) {
+    constexpr int NT = (TS * TS) / SW;
+    const int tid = threadIdx.x, lane = tid & 31;
+    unsigned live = 0;
+#pragma unroll
+    for (int j = 0; j < SW; ++j)
+        if (row < rlim && col0 + j < clim && !(row == pin_r && col0 + j == pin_c)) live |= 1u << j;
+    bool dirty0 = (inmask & IN_ALL) != 0;
+    dirty0 |= (inmask & (IN_N | IN_NW | IN_NE)) && row == 0;
+    dirty0 |= (inmask & (IN_S | IN_SW | IN_SE)) && row == TS - 1;
+    dirty0 |= (inmask & (IN_W | IN_NW | IN_SW)) && col0 == 0;
+    dirty0 |= (inmask & (IN_E | IN_NE | IN_SE)) && col0 == TS - SW;
+    // this thread's SW bytes of the two maps (aligned: col0 is a multiple of SW)
+    unsigned char *myd = s_dirty + row * TS + col0, *myc = s_chgmap + row * TS + col0;
+    int cnt_changed = 0;
+    bool first = true;
+    for (;;) {
+        const int par = iters & 1;
+        // (1) my marked elements; the maps start clean with the first round
+        unsigned dmask = 0;
+        if (first) {
+            dmask = dirty0 ? (1u << SW) - 1u : 0u;
+            if (SW == 4) *(unsigned *) myc = 0u; else *(unsigned short *) myc = 0;
+        } else {
+            const unsigned bytes = (SW == 4) ? *(volatile unsigned *) myd : (unsigned) *(volatile unsigned short *) myd;
+#pragma unroll
+            for (int j = 0; j < SW; ++j)
+                if ((bytes >> (8 * j)) & 0xffu) dmask |= 1u << j;
+        }
+        if (SW == 4) *(unsigned *) myd = 0u; else *(unsigned short *) myd = 0;
+        dmask &= live;
+        first = false;
+        // (2) compaction (as relax_tile_compact)
+        const int my = __popc(dmask);
+        int incl = my;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += t;
+        }
+        const int wtot = __shfl_sync(0xffffffffu, incl, 31);
+        int wbase = 0;
+        if (lane == 31 && wtot) wbase = atomicAdd(&s_n[par], wtot);
+        wbase = __shfl_sync(0xffffffffu, wbase, 31);
+        int pos = wbase + incl - my;
+#pragma unroll
+        for (int j = 0; j < SW; ++j)
+            if ((dmask >> j) & 1u) s_list[pos++] = (unsigned short) (row * TS + col0 + j);
+        __syncthreads();
+        const int n = *(volatile int *) &s_n[par];
+        if (n == 0) {
+            if (tid == 0) s_n[par ^ 1] = 0;
+            break;
+        }
+        // (3) one element per thread; a lowered element marks the neighbours it has read as higher
+        for (int i = tid; i < n; i += NT) {
+            const int e = s_list[i];
+            const int r = e >> 5, c = e & 31;
+            const volatile float *wb = sg + r * GP + c;
+            Nbr8 nb;
+            nb.nw = wb[0]; nb.n = wb[1]; nb.ne = wb[2];
+            nb.w = wb[GP]; const float cur = wb[GP + 1]; nb.e = wb[GP + 2];
+            nb.sw = wb[2 * GP]; nb.s = wb[2 * GP + 1]; nb.se = wb[2 * GP + 2];
+            float v;
+            if (KIND == TASI_KIND_DFM) v = dfm_cell(nb, sc[r * CP + c]);
+            else {
+                const float tl = sc[r * CP + c], tr = sc[r * CP + c + 1], bl = sc[(r + 1) * CP + c], br = sc[(r + 1) * CP + c + 1];
+                v = (KIND == TASI_KIND_FD) ? fd_node(nb, tl, tr, bl, br) : mfd_node(nb, tl, tr, bl, br);
+            }
+            if (v < cur) {
+                sg[(r + 1) * GP + c + 1] = v;
+                s_chgmap[e] = 1;
+                ++cnt_changed;
+                unsigned char *dm = s_dirty + e;
+                const bool up = r > 0, dn = r < TS - 1, lf = c > 0, rt = c < TS - 1;
+                if (up && lf && nb.nw > v) dm[-TS - 1] = 1;
+                if (up && nb.n > v) dm[-TS] = 1;
+                if (up && rt && nb.ne > v) dm[-TS + 1] = 1;
+                if (lf && nb.w > v) dm[-1] = 1;
+                if (rt && nb.e > v) dm[1] = 1;
+                if (dn && lf && nb.sw > v) dm[TS - 1] = 1;
+                if (dn && nb.s > v) dm[TS] = 1;
+                if (dn && rt && nb.se > v) dm[TS + 1] = 1;
+            }
+            ++evals;
+        }
+        if (tid == 0) s_n[par ^ 1] = 0;  // the next round's counter; nobody adds to it before the barrier below
+        __syncthreads();
+        ++iters;
+    }
+    // what the owner writes back: the final values of its strip and which of them changed during the visit
+    __syncthreads();
+    const unsigned cb = (SW == 4) ? *(volatile unsigned *) myc : (unsigned) *(volatile unsigned short *) myc;
+    chg = 0;
+#pragma unroll
+    for (int j = 0; j < SW; ++j) {
+        if ((cb >> (8 * j)) & 0xffu) chg |= 1u << j;
+        w[1][j + 1] = *(const volatile float *) (sg + (row + 1) * GP + col0 + 1 + j);
+    }
+    return cnt_changed;
+}
+
 // ---- in-tile relaxation, compacted inside each warp (CMP = 2) ------------------------------------------------------------
 // As relax_tile_compact, but the dirty elements are compacted per WARP (a warp owns SW whole rows of the tile): ballot-free
 // prefix sum over the lanes, a per-warp list in shared memory, lane i evaluates the warp's i-th dirty element. No CTA
@@ -1257,6 +1372,8 @@ solver_kernel(GridDesc d, const __grid_constant__ TmaMaps tm) {
     __shared__ unsigned short s_list[CMP ? TS * TS : 1];  // compacted relaxation: the dirty elements of a round (CMP = 2:
                                                           // one list of 32 * SW entries per warp)
     __shared__ int s_n[2];                // ... and how many (two counters, alternating by round)
+    __shared__ __align__(16) unsigned char s_dirty[CMP == 3 ? TS * TS : 4];   // CMP = 3: elements marked for the next round
+    __shared__ __align__(16) unsigned char s_chgmap[CMP == 3 ? TS * TS : 4];  // ... and elements changed during the visit
     __shared__ __align__(128) float s_land[TMA ? (TS + 2) * TMA_GW : 1];        // TMA landing buffers
     __shared__ __align__(128) unsigned char s_cland[TMA ? (TS + 1) * TMA_CW : 16];
     __shared__ __align__(8) uint64_t s_bar;
@@ -1427,7 +1544,10 @@ solver_kernel(GridDesc d, const __grid_constant__ TmaMaps tm) {
             for (int a2 = 0; a2 < WIN_R; ++a2)
 #pragma unroll
                 for (int b2 = 0; b2 < WIN_C; ++b2) w[a2][b2] = 0.0f;
-            if (CMP == 2 && MODE == 0)
+            if (CMP == 3 && MODE == 0)
+                n_changed += relax_tile_push<KIND, SW>(sg, sc, s_list, s_n, s_dirty, s_chgmap, s_inmask, row, col0, rlim, clim,
+                                                       pin_r, pin_c, w, chg, it, ev);
+            else if (CMP == 2 && MODE == 0)
                 n_changed += relax_tile_wcompact<KIND, SW>(sg, sc, s_list, s_inmask, row, col0, rlim, clim, pin_r, pin_c, w,
                                                            chg, it, ev);
             else if (CMP == 1 && MODE == 0)

@@ -1141,22 +1141,24 @@ __device__ __forceinline__ int relax_tile_push(float *sg, const float *sc, unsig
         if (SW == 4) *(unsigned *) myd = 0u; else *(unsigned short *) myd = 0;
         dmask &= live;
         first = false;
-        // (2) compaction (as relax_tile_compact)
-        const int my = __popc(dmask);
-        int incl = my;
+        // (2) compaction (as relax_tile_compact); a warp without a marked element has nothing to add
+        if (__any_sync(0xffffffffu, dmask != 0u)) {
+            const int my = __popc(dmask);
+            int incl = my;
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const int t = __shfl_up_sync(0xffffffffu, incl, o);
-            if (lane >= o) incl += t;
+            for (int o = 1; o < 32; o <<= 1) {
+                const int t = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o) incl += t;
+            }
+            const int wtot = __shfl_sync(0xffffffffu, incl, 31);
+            int wbase = 0;
+            if (lane == 31) wbase = atomicAdd(&s_n[par], wtot);
+            wbase = __shfl_sync(0xffffffffu, wbase, 31);
+            int pos = wbase + incl - my;
+#pragma unroll
+            for (int j = 0; j < SW; ++j)
+                if ((dmask >> j) & 1u) s_list[pos++] = (unsigned short) (row * TS + col0 + j);
         }
-        const int wtot = __shfl_sync(0xffffffffu, incl, 31);
-        int wbase = 0;
-        if (lane == 31 && wtot) wbase = atomicAdd(&s_n[par], wtot);
-        wbase = __shfl_sync(0xffffffffu, wbase, 31);
-        int pos = wbase + incl - my;
-#pragma unroll
-        for (int j = 0; j < SW; ++j)
-            if ((dmask >> j) & 1u) s_list[pos++] = (unsigned short) (row * TS + col0 + j);
         __syncthreads();
         const int n = *(volatile int *) &s_n[par];
         if (n == 0) {

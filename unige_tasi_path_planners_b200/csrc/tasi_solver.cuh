@@ -1357,9 +1357,10 @@ constexpr int C_ROWS_NODE = TS + 1, C_ROWS_CELL = TS;
 // TMA = 1: the windows are staged by cp.async.bulk.tensor.2d (see "TMA staging" above) instead of vector loads.
 template <int KIND, int MODE, int SW, int CMP = 0, int TMA = 0>
 #ifndef CMP1_BLOCKS
-#define CMP1_BLOCKS 2  // resident CTAs per SM the CTA-list instances with 4-element strips are compiled for
+#define CMP1_BLOCKS 3  // resident CTAs per SM the CTA-list instances with 4-element strips are compiled for (80 registers,
+                       // no spills in the pushed-mark instances; run_solver launches 3 per SM on large grids only)
 #endif
-__global__ void __launch_bounds__(1024 / SW, SW == 4 ? ((CMP == 1 && MODE == 0) ? CMP1_BLOCKS : 2) : 1)
+__global__ void __launch_bounds__(1024 / SW, SW == 4 ? ((CMP == 3 && MODE == 0) ? CMP1_BLOCKS : 2) : 1)
 solver_kernel(GridDesc d, const __grid_constant__ TmaMaps tm) {
     constexpr int NT = (TS * TS) / SW, WIN_C = SW + 2;
     constexpr int G_ITERS = (G_VECS + NT - 1) / NT, C_ITERS = (C_ROWS_NODE * GV_PER_ROW + NT - 1) / NT;

@@ -447,6 +447,22 @@ int ensure_cost_stats(tasi_planner *p) {
     return TASI_OK;
 }
 
+// The pushed-mark list instances (80 registers) fit three CTAs per SM. The third one pays on large grids, where the
+// solve is bound by what an SM issues (MFD* 16384^2 101 -> 92 ms, FD* 122 -> 116 ms), and costs on smaller ones, where
+// more workers only inflate the visits (8192^2: 35.2 -> 36.2 / 43.7 -> 47.3 ms): three from 150 k tiles. Every CTA of
+// the launch must be resident, so the count comes from the occupancy of THE instance that is launched.
+// Returns the CTA count of such a launch, 0 = keep p->solver_blocks, < 0 = error.
+int relax_blocks(tasi_planner *p, int mode, int nt) {
+    static const int third_from = [] { const char *e = getenv("TASI_THIRD_CTA_FROM"); return e ? atoi(e) : 150000; }();
+    static const bool own_occ = [] { const char *e = getenv("TASI_OWN_OCC"); return e && atoi(e) != 0; }();
+    if (p->max_blocks > 0 || mode != 0 || p->strip != 4) return 0;
+    if (!(own_occ || (compact_for(p) == 3 && nt >= third_from))) return 0;
+    int occ = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, pick_solver(p->kind, mode, p->strip, compact_for(p)),
+                                                      TS * TS / p->strip, 0) != cudaSuccess) return 0;
+    return std::min(std::max(occ, 1) * p->num_sms, nt);
+}
+
 // Queue the flagged tiles and run the persistent solver in `mode` until the queue drains.
 // Adds the launch's counters to p->stats; *ms = CUDA-event time of the three launches.
 int run_solver(tasi_planner *p, int mode, float *ms, bool resume = false, float limit = INFINITY) {
@@ -477,19 +493,9 @@ int run_solver(tasi_planner *p, int mode, float *ms, bool resume = false, float 
     enqueue_seeds_kernel<<<std::min((nt + 255) / 256, 1024), 256, 0, p->stream>>>(d, ordered);
     arm_solver_kernel<<<1, 1, 0, p->stream>>>(d);
     int nblocks = (p->max_blocks > 0 && p->max_blocks < p->solver_blocks) ? p->max_blocks : p->solver_blocks;
-    // The pushed-mark list instances (80 registers) fit three CTAs per SM. The third one pays on large grids, where the
-    // solve is bound by what an SM issues (MFD* 16384^2 101 -> 92 ms, FD* 122 -> 116 ms), and costs on smaller ones, where
-    // more workers only inflate the visits (8192^2: 35.2 -> 36.2 / 43.7 -> 47.3 ms): three from 150 k tiles. Every CTA of
-    // the launch must be resident, so the count comes from the occupancy of THIS instance.
-    static const int third_from = [] { const char *e = getenv("TASI_THIRD_CTA_FROM"); return e ? atoi(e) : 150000; }();
-    static const bool own_occ = [] { const char *e = getenv("TASI_OWN_OCC"); return e && atoi(e) != 0; }();
-    if (p->max_blocks <= 0 && mode == 0 && p->strip == 4 && p->band_rt == 0 &&
-        (own_occ || (compact_for(p) == 3 && nt >= third_from))) {
-        int occ = 0;
-        CU_TRY(p, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, pick_solver(p->kind, mode, p->strip, compact_for(p)),
-                                                                TS * TS / p->strip, 0));
-        nblocks = std::min(std::max(occ, 1) * p->num_sms, nt);
-        p->stats.solver_blocks = nblocks;
+    {
+        const int rb = relax_blocks(p, mode, nt);
+        if (rb > 0) { nblocks = rb; p->stats.solver_blocks = nblocks; }
     }
     pick_solver(p->kind, mode, p->strip, compact_for(p))<<<nblocks, TS * TS / p->strip, 0, p->stream>>>(d, p->tm);
     CU_TRY(p, cudaGetLastError());

@@ -489,7 +489,11 @@ int shard_fused_run(tasi_shard *s, int mode) {
         if (mode == 0) seed_keys_kernel<<<std::min((nt + 7) / 8, p->num_sms * 8), 256, 0, p->stream>>>(d);
         enqueue_seeds_kernel<<<std::min((nt + 255) / 256, 1024), 256, 0, p->stream>>>(d, 1);
         const int cap = s->max_blocks > 0 ? s->max_blocks : p->max_blocks;
-        const int nblocks = (cap > 0 && cap < p->solver_blocks) ? cap : p->solver_blocks;
+        int nblocks = (cap > 0 && cap < p->solver_blocks) ? cap : p->solver_blocks;
+        if (cap <= 0) {
+            const int rb = relax_blocks(p, mode, nt);  // a third CTA per SM on large stacks (see relax_blocks)
+            if (rb > 0) nblocks = rb;
+        }
         pick_solver(p->kind, mode, p->strip, compact_for(p))<<<nblocks, TS * TS / p->strip, 0, p->stream>>>(d, p->tm);
         SH_TRY(s, cudaGetLastError());
     }

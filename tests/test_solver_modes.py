@@ -13,13 +13,14 @@ import pytest
 from unige_tasi_path_planners_b200 import synth
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-KNOBS = ("TASI_TMA", "TASI_COMPACT", "TASI_STRIP", "TASI_REL_PASSES", "TASI_DELTA_FACTOR", "TASI_BUCKETS", "TASI_DEFER", "TASI_CHAIN")
+KNOBS = ("TASI_TMA", "TASI_COMPACT", "TASI_STRIP", "TASI_REL_PASSES", "TASI_DELTA_FACTOR", "TASI_BUCKETS", "TASI_DEFER", "TASI_CHAIN", "TASI_SLIDE")
 MODES = [{"TASI_TMA": "1"}, {"TASI_TMA": "1", "TASI_STRIP": "2"}, {"TASI_COMPACT": "0"}, {"TASI_COMPACT": "1"},
          {"TASI_COMPACT": "2"}, {"TASI_COMPACT": "1", "TASI_STRIP": "4"}, {"TASI_COMPACT": "3"},
          {"TASI_COMPACT": "3", "TASI_STRIP": "4"}, {"TASI_STRIP": "4"}, {"TASI_REL_PASSES": "1"},
          {"TASI_REL_PASSES": "32", "TASI_DELTA_FACTOR": "6"}, {"TASI_BUCKETS": "0"}, {"TASI_BUCKETS": "4"},
          {"TASI_BUCKETS": "16", "TASI_DELTA_FACTOR": "3"}, {"TASI_BUCKETS": "60"}, {"TASI_DEFER": "0.5"},
-         {"TASI_DEFER": "0.1", "TASI_DELTA_FACTOR": "8"}, {"TASI_CHAIN": "1"}]
+         {"TASI_DEFER": "0.1", "TASI_DELTA_FACTOR": "8"}, {"TASI_CHAIN": "1"}, {"TASI_SLIDE": "1"},
+         {"TASI_SLIDE": "1", "TASI_DELTA_FACTOR": "2"}]
 
 
 @pytest.fixture(scope="module")

@@ -195,6 +195,11 @@ GridDesc make_desc(const tasi_planner *p) {
     d.rkey = p->rkey;
     static const int chain = [] { const char *e = getenv("TASI_CHAIN"); return e ? atoi(e) : 0; }();
     d.chain = chain;
+    // sliding key window: plain relax launches of an unsharded grid (run_solver switches it off for focused plans,
+    // launches with a limit and resumed ones, which need the quiescent points of the threshold phases)
+    static const int slide = [] { const char *e = getenv("TASI_SLIDE"); return e ? atoi(e) : 0; }();
+    d.slide = (slide && d.nb > 0 && d.nb <= 31 && p->band_rt == 0 && !p->ft && !(p->rkey && p->defer_tiles >= 0.0f)) ? 1 : 0;
+    d.bw = d.nb > 0 ? d.delta / (float) d.nb : 0.0f;
     d.defer_margin = (d.nb > 0 && p->rkey && p->defer_tiles >= 0.0f)
                          ? p->defer_tiles * (float) TS * p->mean_cost : -1.0f;
     d.bqmask = p->bqsize ? p->bqsize - 1 : 0;
@@ -470,6 +475,8 @@ int run_solver(tasi_planner *p, int mode, float *ms, bool resume = false, float 
     if (rcs != TASI_OK) return rcs;
     GridDesc d = make_desc(p);
     if (mode == 1) { d.n_focus = 0; d.nb = 0; d.defer_margin = -1.0f; }
+    if (mode == 1 || d.n_focus > 0 || resume || limit < INFINITY || d.nb <= 0) d.slide = 0;
+    if (d.slide) CU_TRY(p, cudaMemsetAsync(p->far, 0, sizeof(int) * (size_t) p->far_cap, p->stream));  // 0 = slot not written
     static const bool repair_buckets = [] { const char *e = getenv("TASI_REPAIR_BUCKETS"); return !e || atoi(e) != 0; }();
     if (!p->fresh_plan && !repair_buckets) d.nb = 0;
     DevCtl z;
@@ -507,6 +514,9 @@ int run_solver(tasi_planner *p, int mode, float *ms, bool resume = false, float 
 #ifdef TASI_DEBUG_COMPACT
     if (h.kick >= 100000) { p->err = "compact debug flag " + std::to_string(h.kick); return TASI_ERR_STATE; }
 #endif
+    if (d.slide && getenv("TASI_SLIDE_DEBUG"))
+        fprintf(stderr, "slide: abase %d scans %llu far_count %d far_scanned %d jumps %d visits %llu bw %.1f\n", h.abase,
+                h.slide_scans, h.far_count[0], h.far_scanned, h.phases, h.visits, d.bw);
     p->sv_far_sel = h.far_sel;
     p->sv_far_count[0] = std::min(h.far_count[0], p->far_cap);
     p->sv_far_count[1] = std::min(h.far_count[1], p->far_cap);

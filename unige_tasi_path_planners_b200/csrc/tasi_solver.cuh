@@ -71,6 +71,11 @@ struct DevCtl {
     alignas(128) unsigned long long btail[QB_MAX];
     alignas(128) int bcount[QB_MAX];  // published entries of each ring not yet claimed by a popper
     unsigned long long deferred;      // tiles set aside by the upwind deferral
+    // sliding key window (GridDesc::slide): absolute index of the slice the lowest ring stands for, the prefix of the
+    // (append-only) far list already dealt with, and the lock of whoever scans it
+    int abase, far_scanned, scan_lock;
+    unsigned long long slide_scans;
+    alignas(128) int brun[QB_MAX];    // sliding window: tiles being visited that were claimed from each ring
     // patch bookkeeping
     unsigned long long n_changed, n_raised, n_lowered_cells, n_seed_elems;
     unsigned long long halo_lowered;
@@ -125,6 +130,9 @@ struct GridDesc {
     float defer_margin;
     int *rkey;             // TX*TY: the key a running tile was claimed with
     int chain;             // TASI_CHAIN: a CTA goes on with the lowest-keyed neighbour it has just activated (see solver_kernel)
+    // sliding key window (TASI_SLIDE; see "sliding key window" below): ring = (key / bw) mod nb, no threshold phases
+    int slide;
+    float bw;              // ring width = delta / nb
 };
 
 // TMA staging (solver instances with TMA = 1, TASI_TMA=1): the two CUtensorMap (128 opaque bytes each) the kernel takes
@@ -162,6 +170,13 @@ __device__ __forceinline__ int cur_thr_bits(const GridDesc &d);
 // ring of the bucketed near queue for key `kbits` (-1 = the plain ring)
 __device__ __forceinline__ int bucket_of(const GridDesc &d, int kbits) {
     if (d.nb <= 0) return -1;
+    if (d.slide) {  // absolute, cyclic: slice of the key, clamped into the window [base, base + nb)
+        const int a = *(volatile int *) &d.ctl->abase;
+        int si = (kbits == INF_BITS) ? a : (int) (__int_as_float(kbits) * d.inv_bw);
+        si = max(si, a);
+        si = min(si, a + d.nb - 1);
+        return si % d.nb;
+    }
     const int tb = cur_thr_bits(d);
     if (tb == INF_BITS || kbits == INF_BITS) return 0;
     const float x = (__int_as_float(kbits) - (__int_as_float(tb) - d.delta)) * d.inv_bw;
@@ -246,10 +261,35 @@ __device__ inline int q_pop(const GridDesc &d) {
 // current threshold go to the work queue ("near"); the others are parked in the far pile until the queue has
 // drained and the threshold advances by `delta` (a tile-level Delta-stepping order: without it a
 // label-correcting solve revisits each tile dozens of times, with it a few).
-__device__ __forceinline__ int cur_thr_bits(const GridDesc &d) { return *(volatile int *) &d.ctl->thr_bits; }
+// near / far boundary. Sliding window: the window of nb rings above the base slice.
+__device__ __forceinline__ int cur_thr_bits(const GridDesc &d) {
+    if (d.slide) return __float_as_int((float) (*(volatile int *) &d.ctl->abase + d.nb) * d.bw);
+    return *(volatile int *) &d.ctl->thr_bits;
+}
 
 // park a tile whose state already carries ST_FAR; falls back to the queue if the pile is full
 __device__ inline void far_append(const GridDesc &d, int tile) {
+    if (d.slide) {
+        // sliding window: one append-only list of tile + 1 (0 = slot taken, not written yet). The window may pass the
+        // key while the tile is being parked, and a scan may already be beyond this slot: look again after the append
+        // and take the tile back if it has become due (whoever clears ST_FAR owns the push).
+        const int slot = atomicAdd(&d.ctl->far_count[0], 1);
+        if (slot < d.far_cap) {
+            *(volatile int *) &d.far[slot] = tile + 1;
+            __threadfence();
+            atomicAdd(&d.ctl->far_parked, 1ULL);
+            const int k = *(volatile int *) &d.key[tile];
+            if (k < cur_thr_bits(d) && (atomicAnd(&d.state[tile], ~ST_FAR) & ST_FAR)) {
+                q_push_key(d, tile, k);
+                atomicAdd(&d.ctl->pushes, 1ULL);
+            }
+        } else {
+            atomicAnd(&d.state[tile], ~ST_FAR);
+            q_push(d, tile);
+            atomicAdd(&d.ctl->pushes, 1ULL);
+        }
+        return;
+    }
     const int sel = *(volatile int *) &d.ctl->far_sel;
     const int slot = atomicAdd(&d.ctl->far_count[sel], 1);
     if (slot < d.far_cap) {
@@ -292,6 +332,93 @@ __device__ inline bool activate(const GridDesc &d, int tile, int kbits, int dirb
         }
     }
     return false;
+}
+
+// ---- sliding key window (TASI_SLIDE) -----------------------------------------------------------------------------------
+// With the rings the threshold phases are only the trade between a wide band (tiles far up the band run on provisional
+// borders) and many phase barriers (CTAs wait at each). Here there are no phases: ring = (key / bw) mod nb, absolute and
+// cyclic; the window is the nb slices above the BASE slice, which follows the lowest non-empty ring (a popper that finds
+// its tile at offset o > 0 raises the base by o with atomicMax; a push below the base is clamped into the base ring); the
+// near / far boundary is base + nb and moves with it, so a tile activated for the first time — its key lies a tile width
+// or two above the front — is never parked. What lies beyond the window goes to an append-only far list; the popper
+// that moves the base across a multiple of SLIDE_SCAN_EVERY slices scans the list (one scanner at a time) and releases
+// what the window has reached. Hand-over of a parked tile (appender that finds the window has passed it, scanner,
+// promoting activation): whoever clears ST_FAR owns the push. Quiescence (pending == 0) only happens when everything
+// left is parked beyond the window: the base jumps to the lowest parked key.
+constexpr int SLIDE_SCAN_EVERY = 4;
+
+// One pass over the unscanned part of the far list by the 32 lanes of a warp. jump: the grid is quiescent — first move the
+// base to the slice of the lowest parked key. Returns (to every lane) the number of live entries left parked.
+__device__ inline int slide_scan_warp(const GridDesc &d, int lane, bool jump) {
+    DevCtl *c = d.ctl;
+    const unsigned full = 0xffffffffu;
+    // one scanner at a time
+    int got = 0;
+    if (lane == 0) {
+        if (jump) { while (atomicCAS(&c->scan_lock, 0, 1) != 0) __nanosleep(64); got = 1; }
+        else got = atomicCAS(&c->scan_lock, 0, 1) == 0;
+    }
+    got = __shfl_sync(full, got, 0);
+    if (!got) return -1;
+    __threadfence();
+    const int s0 = *(volatile int *) &c->far_scanned;
+    const int n = min(*(volatile int *) &c->far_count[0], d.far_cap);
+    // first slot that is taken but not written yet: the prefix cannot pass it
+    int stop = n;
+    for (int i = s0 + lane; i < n; i += 32)
+        if (*(volatile int *) &d.far[i] == 0) { stop = i; break; }
+    stop = __reduce_min_sync(full, stop);
+    if (jump) {
+        int m = INF_BITS;
+        for (int i = s0 + lane; i < n; i += 32) {
+            const int e = *(volatile int *) &d.far[i];
+            if (e > 0 && (*(volatile int *) &d.state[e - 1] & ST_FAR)) m = min(m, *(volatile int *) &d.key[e - 1]);
+        }
+        m = __reduce_min_sync(full, m);
+        if (lane == 0) {
+            c->far_min_bits = m;
+            if (m != INF_BITS) atomicMax(&c->abase, (int) (__int_as_float(m) * d.inv_bw));
+            atomicAdd(&c->phases, 1);
+            __threadfence();
+        }
+        __syncwarp();
+    }
+    const int thr = cur_thr_bits(d);
+    const bool relall = jump && *(volatile int *) &c->far_min_bits == INF_BITS;  // only tiles without a finite key are left
+    int left = 0;
+    for (int i = s0 + lane; i < n; i += 32) {
+        const int e = *(volatile int *) &d.far[i];
+        if (e <= 0) continue;
+        const int t = e - 1;
+        if (!(*(volatile int *) &d.state[t] & ST_FAR)) continue;  // stale: promoted or taken back meanwhile
+        const int k = *(volatile int *) &d.key[t];
+        if (k < thr || relall) {
+            if (atomicAnd(&d.state[t], ~ST_FAR) & ST_FAR) {
+                q_push_key(d, t, k);
+                atomicAdd(&c->pushes, 1ULL);
+            }
+        } else {
+            ++left;
+            if (i < stop) {  // keep it: behind the new prefix it would never be looked at again, so it moves to the tail
+                const int slot = atomicAdd(&c->far_count[0], 1);
+                if (slot < d.far_cap) *(volatile int *) &d.far[slot] = e;
+                else if (atomicAnd(&d.state[t], ~ST_FAR) & ST_FAR) {  // list full: run it now
+                    q_push_key(d, t, k);
+                    atomicAdd(&c->pushes, 1ULL);
+                }
+            }
+        }
+    }
+    left = __reduce_add_sync(full, left);
+    __threadfence();
+    if (lane == 0) {
+        c->far_scanned = stop;
+        atomicAdd(&c->slide_scans, 1ULL);
+        __threadfence();
+        atomicExch(&c->scan_lock, 0);
+    }
+    __syncwarp();
+    return left;
 }
 
 // The queue has drained and no tile is running: raise the threshold to (lowest parked key + delta) and move
@@ -380,6 +507,28 @@ __device__ inline bool advance_threshold(const GridDesc &d, int *s_red, int tid)
 // again, or end the launch (nothing parked, or everything parked lies beyond the limit).
 __device__ inline void drain_and_advance(const GridDesc &d, int *s_red, int *s_adv, int tid) {
     __syncthreads();
+    if (d.slide) {
+        // sliding window: the count reached 0, so whatever is left is parked beyond the window — the base jumps to the
+        // lowest parked key (slide_scan_warp with jump), until nothing is left anywhere
+        while (*s_adv) {
+            __syncthreads();
+            if (tid == 0) atomicAdd(&d.ctl->pending, 1);  // hold the count while tiles are being pushed
+            int left = 0;
+            if (tid < 32) left = slide_scan_warp(d, tid, true);
+            __syncthreads();
+            if (tid == 0) {
+                int more = 0;
+                if (atomicSub(&d.ctl->pending, 1) == 1) {  // nothing was pushed (or all of it already finished)
+                    if (left > 0) more = 1;
+                    else { __threadfence(); atomicExch(&d.ctl->done, 1); }
+                }
+                if (*(volatile int *) &d.ctl->error) more = 0;
+                *s_adv = more;
+            }
+            __syncthreads();
+        }
+        return;
+    }
     while (*s_adv) {
         __syncthreads();
         const long long ca0 = clock64();
@@ -694,16 +843,23 @@ __device__ inline int q_pop_fused(const GridDesc &d, unsigned long long *ticket)
 // then a ticket of its head, whose slot is filled or about to be. Nobody commits to a ring that may never be fed again.
 // Lane 31 watches the plain ring (entries queued without an order before the launch). Returns the same value to every lane.
 // fused0: CTA 0 of a fused multi-GPU launch, which also serves the coordinator (returns -2: call fused_service).
-__device__ inline int q_pop_warp(const GridDesc &d, int lane, bool fused0) {
+__device__ inline int q_pop_warp(const GridDesc &d, int lane, bool fused0, int *ring_out = nullptr) {
     DevCtl *c = d.ctl;
     const unsigned full = 0xffffffffu;
-    const bool m0 = lane < 31 && lane < d.nb, m1 = lane < 31 && lane + 31 < d.nb;  // rings lane and lane + 31
+    const bool m0 = lane < 31 && lane < d.nb, m1 = !d.slide && lane < 31 && lane + 31 < d.nb;  // rings lane and lane + 31
     unsigned long long t0 = 0, sum0 = 0;
     unsigned ns = 32, polls = 0;
     for (;;) {
-        int cnt0 = 0, cnt1 = 0;
+        int cnt0 = 0, cnt1 = 0, run0 = 0;
         unsigned long long ph = 0, pt = 0;
-        if (m0) cnt0 = *(volatile int *) &c->bcount[lane];
+        // sliding window (nb <= 31): lane l looks at the ring l slices above the base, so the lowest lane is the lowest key
+        int abase = 0, rot = lane;
+        if (d.slide) {
+            abase = __shfl_sync(full, *(volatile int *) &c->abase, 0);
+            rot = (abase + lane) % d.nb;
+            if (m0) run0 = *(volatile int *) &c->brun[rot];
+        }
+        if (m0) cnt0 = *(volatile int *) &c->bcount[rot];
         if (m1) cnt1 = *(volatile int *) &c->bcount[lane + 31];
         if (lane == 31) {
             ph = *(volatile unsigned long long *) &c->head;
@@ -711,19 +867,39 @@ __device__ inline int q_pop_warp(const GridDesc &d, int lane, bool fused0) {
         }
         const unsigned ma = __ballot_sync(full, cnt0 > 0), mb = __ballot_sync(full, cnt1 > 0);
         const unsigned mp = __ballot_sync(full, lane == 31 && ph < pt);
+        if (d.slide) {
+            // the window base follows the lowest ring that holds a queued tile OR a tile being visited (a visit pushes at
+            // or above its own slice, so nothing can appear below such a ring); crossing a multiple of
+            // SLIDE_SCAN_EVERY slices, this warp also looks through the far list
+            const unsigned mr = __ballot_sync(full, cnt0 > 0 || run0 > 0);
+            const int lowest = mr ? __ffs(mr) - 1 : 0;
+            if (lowest > 0) {
+                int scan = 0;
+                if (lane == 0) {
+                    const int old = atomicMax(&c->abase, abase + lowest);
+                    scan = old < abase + lowest && (abase + lowest) / SLIDE_SCAN_EVERY > old / SLIDE_SCAN_EVERY &&
+                           *(volatile int *) &c->far_count[0] > *(volatile int *) &c->far_scanned;
+                }
+                if (__shfl_sync(full, scan, 0)) slide_scan_warp(d, lane, false);
+            }
+        }
         if (ma | mb | mp) {
             const int src = ma ? __ffs(ma) - 1 : (mb ? __ffs(mb) - 1 : 31);
-            const int b = ma ? src : src + 31;
+            const int b = ma ? (d.slide ? (abase + src) % d.nb : src) : src + 31;
             int v = 0;
             if (lane == src) {
                 volatile int *slot = nullptr;
                 if (!(ma | mb)) {
                     if (atomicCAS(&c->head, ph, ph + 1ULL) == ph) slot = &d.queue[(unsigned) ph & d.qmask];
-                } else if (atomicSub(&c->bcount[b], 1) > 0) {
-                    const unsigned long long h = atomicAdd(&c->bhead[b], 1ULL);
-                    slot = &d.bq[(size_t) b * (d.bqmask + 1u) + ((unsigned) h & d.bqmask)];
                 } else {
-                    atomicAdd(&c->bcount[b], 1);  // spent meanwhile: give the unit back
+                    if (d.slide) atomicAdd(&c->brun[b], 1);  // before the count drops: the ring never looks idle in between
+                    if (atomicSub(&c->bcount[b], 1) > 0) {
+                        const unsigned long long h = atomicAdd(&c->bhead[b], 1ULL);
+                        slot = &d.bq[(size_t) b * (d.bqmask + 1u) + ((unsigned) h & d.bqmask)];
+                    } else {
+                        atomicAdd(&c->bcount[b], 1);  // spent meanwhile: give the unit back
+                        if (d.slide) atomicSub(&c->brun[b], 1);
+                    }
                 }
                 if (slot) {
                     while ((v = *slot) == 0) {}
@@ -731,7 +907,10 @@ __device__ inline int q_pop_warp(const GridDesc &d, int lane, bool fused0) {
                 }
             }
             v = __shfl_sync(full, v, src);
-            if (v) return v - 1;
+            if (v) {
+                if (ring_out && lane == 0) *ring_out = (ma | mb) ? b : -1;
+                return v - 1;
+            }
             continue;  // somebody else took it: look again
         }
         int stop = 0;
@@ -1368,6 +1547,7 @@ solver_kernel(GridDesc d, const __grid_constant__ TmaMaps tm) {
     __shared__ float sc[(TS + 1) * CP];   // cell costs as float, INF = obstacle
     __shared__ int s_tile, s_inmask, s_again, s_adv;
     __shared__ int s_chain, s_chain_key;  // chaining: the neighbour this CTA goes on with (-1: none)
+    __shared__ int s_ring;                // sliding window: the ring the tile being visited was claimed from (-1: none)
     if (threadIdx.x == 0) s_chain = -1;
     __shared__ int s_kmin[8];             // per neighbour direction: lowest changed value it will read (bits)
     __shared__ int s_red[MAX_WARPS];
@@ -1417,7 +1597,8 @@ solver_kernel(GridDesc d, const __grid_constant__ TmaMaps tm) {
             if (t >= 0 && d.defer_margin >= 0.0f && !defer_or_run(d, t, tid)) t = -1;
             if (t < 0) {
                 do {
-                    t = q_pop_warp(d, tid, fused && blockIdx.x == 0);
+                    if (tid == 0) s_ring = -1;
+                    t = q_pop_warp(d, tid, fused && blockIdx.x == 0, &s_ring);
                 } while (t >= 0 && d.defer_margin >= 0.0f && !defer_or_run(d, t, tid));
             }
             if (tid == 0) {
@@ -1714,7 +1895,11 @@ solver_kernel(GridDesc d, const __grid_constant__ TmaMaps tm) {
             continue;
         }
         if (s_chain >= 0) continue;  // chaining: the pending count of this visit passes to the kept neighbour
-        if (tid == 0) s_adv = (atomicSub(&d.ctl->pending, 1) == 1) ? 1 : 0;
+        if (tid == 0) {
+            // sliding window: the visit is over and its activations are queued — its ring may be passed by the base
+            if (d.slide && s_ring >= 0) atomicSub(&d.ctl->brun[s_ring], 1);
+            s_adv = (atomicSub(&d.ctl->pending, 1) == 1) ? 1 : 0;
+        }
         drain_and_advance(d, s_red, &s_adv, tid);
     }
 
@@ -1815,7 +2000,7 @@ __global__ void enqueue_seeds_kernel(GridDesc d, int ordered) {
                 if (ordered) {
                     const int sel = c->far_sel;
                     const int slot = atomicAdd(&c->far_count[sel], 1);
-                    if (slot < d.far_cap) { d.far[sel * d.far_cap + slot] = t; continue; }
+                    if (slot < d.far_cap) { d.far[sel * d.far_cap + slot] = d.slide ? t + 1 : t; continue; }
                     atomicAnd(&d.state[t], ~ST_FAR);  // pile full: run it now
                 }
                 atomicAdd(&c->pending, 1);

@@ -169,7 +169,7 @@ def test_gpu_extractor_class_mirrors_the_reference_members():
 
 
 @pytest.mark.gpu
-def test_gpu_batch_of_walks_equals_single_walks():
+def test_gpu_batch_of_walks_equals_single_walks(oracle):
     start, goal = (100.0, 90.0), (10.0, 12.0)
     cmap = synth.synth_map(9, 128, 128, 10, start, goal)
     p = gpu_planner(2, cmap, start, goal)
@@ -183,6 +183,17 @@ def test_gpu_batch_of_walks_equals_single_walks():
         assert np.array_equal(m["path"], one[0]) and np.array_equal(m["costs"], one[1])
         assert m["status"] == one[4] and np.float32(m["total_cost"]) == np.float32(one[2])
     assert sum(m["status"] == 0 for m in many) >= 30
+    # ... and against the reference's own extractor (oracle/_ref, where it was built) for a few of them: the host build
+    # of the product's walk above is a stand-in for it, test_extract pins the two to each other
+    if oracle.ref_available():
+        r = oracle.RefPlanner(2, 1)
+        r.set_map(cmap)
+        r.set_goal(*goal)
+        for s, m in list(zip(starts, many))[:6]:
+            r.set_start(*s)
+            xy, cost, dist, _ = r.extract(field=field, max_steps=4000)
+            assert np.array_equal(xy, m["path"]) and np.float32(cost) == np.float32(m["total_cost"])
+        r.close()
     p.close()
 
 

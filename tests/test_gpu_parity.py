@@ -233,6 +233,14 @@ def test_stacked_batch_equals_single_plans(oracle, kind):
         hw = hostops.host_extract(kind == 1, sb.field(i), m, s, g, 255, 2000)
         assert np.array_equal(walks[i]["path"], hw[0]) and np.array_equal(walks[i]["costs"], hw[1]), i
         assert walks[i]["status"] == hw[4] and (kind == 1 or hw[4] == 0)
+        if oracle.ref_available() and kind != 1:  # the reference's own extractor over the same block (oracle/_ref)
+            r = oracle.RefPlanner(kind, 1)
+            r.set_map(m)
+            r.set_start(*s)
+            r.set_goal(*g)
+            xy, cost, _, _ = r.extract(field=sb.field(i), max_steps=2000)
+            r.close()
+            assert np.array_equal(xy, walks[i]["path"]), i
     # a replan on the stack: patch map 1's block, every block still equals its own from-scratch plan
     patch = synth.synth_rows(77, 0, 20, 30, 20)
     sb.p.patch_map(patch, 1 * (L + 1) + 10, 40)

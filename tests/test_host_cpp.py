@@ -94,6 +94,14 @@ def test_plan_demo_matches_oracle(demo, oracle, kind, tmp_path):
         path = np.fromfile(dump + "." + what + ".path", np.float32).reshape(-1, 2)
         hw = hostops.host_extract(k == 1, got, cm, start if what == "plan" else (8.0, 8.0), goal, 255, 20)
         assert np.array_equal(path, hw[0])
+        if oracle.ref_available() and k != 1:  # the reference's own extractor over the dumped field (oracle/_ref)
+            rp = oracle.RefPlanner(k, 1)
+            rp.set_map(cm)
+            rp.set_start(*(start if what == "plan" else (8.0, 8.0)))
+            rp.set_goal(*goal)
+            xy, _, _, _ = rp.extract(field=got, max_steps=20)
+            rp.close()
+            assert np.array_equal(xy, path)
         line = lines[0 if what == "plan" else 1]
         assert line["path_points"] == len(path) and line["path_cost"] == pytest.approx(hw[2], rel=1e-6)
     assert lines[1]["num_nodes_updated"] > 0 and lines[0]["tile_visits"] > 0
